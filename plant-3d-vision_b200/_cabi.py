@@ -1,0 +1,72 @@
+"""ctypes binding of ``libbp_b200.so`` (C ABI declared in ``include/bp_b200.h``).
+
+This is the only place the package touches native code.  A missing library is a hard error:
+there is deliberately no CPU / numpy / torch fallback for the hot path.
+"""
+import ctypes
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libbp_b200.so")
+
+MODE_CARVING, MODE_AVERAGING = 0, 1
+MASK_U8, MASK_I32, MASK_F32, MASK_U16 = 0, 1, 2, 3
+FLAG_INVERT, FLAG_BOOL_INVERT, FLAG_DEVICE_MASKS = 1, 2, 4
+
+# every symbol include/bp_b200.h declares; tests check the library exports all of them
+SYMBOLS = [
+    "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
+    "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_timing",
+    "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version",
+]
+
+_lib = None
+
+
+class BackprojectionError(RuntimeError):
+    """A libbp_b200 call failed (message from bp_last_error)."""
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (nvcc, sm_100a). plant3dvision_b200 has no CPU fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        c_f = ctypes.POINTER(ctypes.c_float)
+        c_i = ctypes.POINTER(ctypes.c_int32)
+        vp = ctypes.c_void_p
+        L.bp_create.argtypes = [ctypes.POINTER(vp), c_i, ctypes.c_int32, ctypes.c_int32, c_f,
+                                ctypes.c_float, ctypes.c_int, ctypes.c_float, ctypes.c_int]
+        L.bp_destroy.argtypes = [vp]
+        L.bp_clear.argtypes = [vp]
+        L.bp_process_view.argtypes = [vp, c_f, c_f, c_f, vp, ctypes.c_int32, ctypes.c_int32,
+                                      ctypes.c_int, ctypes.c_uint32, c_f]
+        L.bp_process_views.argtypes = [vp, ctypes.c_int32, c_f, ctypes.POINTER(vp), c_i,
+                                       ctypes.c_int, ctypes.c_uint32, c_f]
+        L.bp_get_values.argtypes = [vp, vp]
+        L.bp_get_values_device.argtypes = [vp, vp]
+        L.bp_device_state.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_int64), c_i]
+        L.bp_sync.argtypes = [vp]
+        L.bp_timing.argtypes = [vp, c_f, c_f, ctypes.POINTER(ctypes.c_int64)]
+        L.bp_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
+        L.bp_host_free.argtypes = [vp]
+        L.bp_last_error.restype = ctypes.c_char_p
+        L.bp_version.restype = ctypes.c_char_p
+        for name in SYMBOLS:
+            if name not in ("bp_last_error", "bp_version"):
+                getattr(L, name).restype = ctypes.c_int
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().bp_last_error().decode("utf-8", "replace")
+        if rc == -1:
+            raise ValueError(f"libbp_b200: {msg}")
+        if rc == -3:
+            raise MemoryError(f"libbp_b200: {msg}")
+        raise BackprojectionError(f"libbp_b200 (code {rc}): {msg}")

@@ -1,0 +1,401 @@
+#!/usr/bin/env python3
+# -*- coding: utf-8 -*-
+"""
+plant3dvision_b200.cl
+_____________________
+
+Drop-in for the ``Backprojection`` class of ``plant3dvision.cl`` (reference:
+plant3dvision/cl.py:47-311): same constructor, attributes, methods, return dtypes and
+shapes.  The OpenCL context / programs of the reference (cl.py:29-44) are replaced by
+``libbp_b200.so`` (sm_100a CUDA behind the C ABI of ``include/bp_b200.h``).
+
+Differences a caller can observe, all additive:
+
+* ``process_label`` / ``process_fileset`` hand all views of a label to ONE fused kernel
+  (``bp_process_views``) instead of one launch + ``finish()`` per view (cl.py:223-226); the
+  result is bit-identical to the per-view loop.
+* keyword-only ``device`` and ``i_range`` constructor arguments select the GPU and an axis-0
+  slab of the grid (multi-GPU sharding, see ``parallel.py``).
+* ``get_volume`` is an alias of ``get_values``; ``close()`` / context manager free the device
+  memory deterministically.
+
+There is no CPU fallback: without the built library or a CUDA device, construction raises.
+"""
+import ctypes
+import logging
+import weakref
+
+import numpy as np
+
+from . import _cabi
+
+logger = logging.getLogger(__name__)
+
+EPS = 1e-10  # cl.py:35
+
+_F = ctypes.POINTER(ctypes.c_float)
+_I = ctypes.POINTER(ctypes.c_int32)
+
+#: views handed to one bp_process_views call by process_label (host memory bound)
+MAX_VIEWS_PER_CALL = 256
+
+
+def img_as_float32(mask):
+    """Host restatement of what ``skimage.util.img_as_float32`` does to the mask dtypes this
+    path meets (used at cl.py:205-206): unsigned ints are scaled by ``1/max`` in float32,
+    bool becomes 0/1, floats are cast."""
+    mask = np.asarray(mask)
+    if mask.dtype == np.float32:
+        return mask
+    if mask.dtype == np.bool_:
+        return mask.astype(np.float32)
+    if mask.dtype.kind == "u":
+        return np.multiply(mask, 1.0 / np.iinfo(mask.dtype).max, dtype=np.float32)
+    if mask.dtype.kind == "f":
+        return mask.astype(np.float32)
+    if mask.dtype.kind == "i":
+        # skimage maps signed ints to [-1, 1]; masks never come this way in the pipeline
+        info = np.iinfo(mask.dtype)
+        out = np.multiply(mask, 1.0 / info.max, dtype=np.float32)
+        return np.maximum(out, -1.0, out=out)
+    raise TypeError(f"Unsupported mask dtype {mask.dtype}")
+
+
+class _PinnedArray:
+    """numpy view over page-locked host memory from ``bp_host_alloc``."""
+
+    def __init__(self, shape, dtype):
+        n_bytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(dtype).itemsize
+        ptr = ctypes.c_void_p()
+        _cabi.check(_cabi.lib().bp_host_alloc(ctypes.byref(ptr), n_bytes))
+        self._ptr = ptr
+        self._fin = weakref.finalize(self, _cabi.lib().bp_host_free, ptr)
+        buf = (ctypes.c_char * max(n_bytes, 1)).from_address(ptr.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape, dtype=np.int64))).reshape(shape)
+        # keep the allocation alive as long as any view of the array is
+        self._keep = buf
+        buf._owner = self
+
+
+class Backprojection(object):
+    """Back-projection onto a voxel volume (space carving or averaging).
+
+    Same public surface as the reference class (cl.py:47-311).
+
+    Parameters
+    ----------
+    shape : list
+        Shape ``[nx, ny, nz]`` of the voxel volume.
+    origin : list
+        World position of voxel ``(0, 0, 0)``.
+    voxel_size : float
+        Size of a voxel.
+    type : {'carving', 'averaging'}
+        Kernel to use (cl.py:145-152); anything else raises ``ValueError``.
+    default_value : float
+        Seed of the grid (cl.py:173).
+    labels : list, optional
+        Labels of an ML pipeline mask set, or ``None``.
+    log : bool
+        For averaging, accumulate ``log(1e-10 + p)`` (cl.py:207-208).
+    device : int, optional (keyword only)
+        CUDA device ordinal; defaults to ``LOCAL_RANK`` (under torchrun) or 0.
+    i_range : (int, int), optional (keyword only)
+        Hold only planes ``[i0, i1)`` of axis 0 (slab sharding). ``get_values`` then returns
+        ``[i1 - i0, ny, nz]``.
+    """
+
+    def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
+                 *, device=None, i_range=None):
+        self.shape = shape
+        self.origin = origin
+        self.voxel_size = voxel_size
+        self.default_value = default_value
+        self.log = log
+        self.labels = labels
+        if type == "carving":
+            self.dtype = np.int32
+            self._mode = _cabi.MODE_CARVING
+        elif type == "averaging":
+            self.dtype = np.float32
+            self._mode = _cabi.MODE_AVERAGING
+        else:
+            raise ValueError(f"Unknown kernel type {type}, valid values are 'averaging' or 'carving'!")
+        self.kernel = type  # the reference stores the OpenCL kernel object here
+        if device is None:
+            import os
+            device = int(os.environ.get("LOCAL_RANK", "0"))
+        self.device = int(device)
+        nx = int(self.shape[0])
+        self.i_range = (0, nx) if i_range is None else (int(i_range[0]), int(i_range[1]))
+        self.local_shape = [self.i_range[1] - self.i_range[0], int(self.shape[1]), int(self.shape[2])]
+
+        buff_size = int(np.prod(self.local_shape, dtype=np.int64)) * 4
+        logger.info(f"Buffer shape is {self.shape}")
+        logger.info(f"Required memory for buffer is {buff_size / 2 ** 20:.1f} MiB!")
+
+        self._h = None
+        self._values = None
+        self._lut_cache = {}
+        self.init_buffers()
+
+    # -- buffers ---------------------------------------------------------------------------
+    def init_buffers(self):
+        """Create the device grid seeded with ``default_value`` (cl.py:171-188)."""
+        self.close()
+        shape = (ctypes.c_int32 * 3)(*[int(s) for s in self.shape])
+        origin = (ctypes.c_float * 3)(*[float(np.float32(o)) for o in self.origin])
+        h = ctypes.c_void_p()
+        _cabi.check(_cabi.lib().bp_create(ctypes.byref(h), shape, self.i_range[0], self.i_range[1], origin,
+                                          float(np.float32(self.voxel_size)), self._mode,
+                                          float(self.default_value), self.device))
+        self._h = h
+        self._fin = weakref.finalize(self, _cabi.lib().bp_destroy, h)
+        return
+
+    @property
+    def values_h(self):
+        """Host buffer ``get_values`` fills (pinned; allocated on first use)."""
+        if self._values is None:
+            self._values = _PinnedArray(tuple(self.local_shape), self.dtype)
+            if self._values.array.size:
+                self._values.array[...] = self.default_value
+        return self._values.array
+
+    def close(self):
+        """Free the device memory now (also done by the garbage collector)."""
+        if getattr(self, "_h", None) is not None:
+            self._fin.detach()
+            _cabi.lib().bp_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _handle(self):
+        if self._h is None:
+            raise RuntimeError("Backprojection is closed")
+        return self._h
+
+    # -- mask conversion -------------------------------------------------------------------
+    def _lut(self, kind):
+        """256-entry table of what cl.py:205-208 makes of each byte value."""
+        key = (kind, bool(self.log))
+        if key not in self._lut_cache:
+            if kind == "bool":
+                lut = np.zeros(256, dtype=np.float32)
+                lut[1:] = 1.0
+            else:
+                lut = img_as_float32(np.arange(256, dtype=np.uint8))
+            if self.log:
+                lut = np.log(EPS + lut)
+            self._lut_cache[key] = np.ascontiguousarray(lut, dtype=np.float32)
+        return self._lut_cache[key]
+
+    def _prepare(self, mask, invert):
+        """-> (contiguous array, mask_dtype code, flags, lut or None), applying on the host only
+        what the device cannot do bit-identically."""
+        mask = np.asarray(mask)
+        if mask.ndim != 2:
+            raise ValueError(f"mask must be a 2-D array, got shape {mask.shape}")
+        flags = 0
+        lut = None
+        if self._mode == _cabi.MODE_CARVING:
+            # cl.py:215 casts to int32 and the kernel tests `== 0`
+            if mask.dtype == np.bool_:
+                arr, code = mask.view(np.uint8), _cabi.MASK_U8
+                flags |= _cabi.FLAG_BOOL_INVERT if invert else 0
+            elif mask.dtype == np.uint8:
+                arr, code = mask, _cabi.MASK_U8
+                flags |= _cabi.FLAG_INVERT if invert else 0
+            elif mask.dtype == np.uint16:
+                arr, code = mask, _cabi.MASK_U16
+                flags |= _cabi.FLAG_INVERT if invert else 0
+            elif mask.dtype.kind in "iu":
+                if invert:
+                    mask = np.invert(mask)
+                arr, code = mask.astype(np.int32), _cabi.MASK_I32
+            elif mask.dtype.kind == "f":
+                if invert:
+                    np.invert(mask)  # raises TypeError exactly as the reference would
+                arr, code = mask.astype(np.float32, copy=False), _cabi.MASK_F32
+            else:
+                raise TypeError(f"Unsupported mask dtype {mask.dtype}")
+        else:
+            if mask.dtype == np.bool_:
+                arr, code, lut = mask.view(np.uint8), _cabi.MASK_U8, self._lut("bool")
+                flags |= _cabi.FLAG_BOOL_INVERT if invert else 0
+            elif mask.dtype == np.uint8:
+                arr, code, lut = mask, _cabi.MASK_U8, self._lut("u8")
+                flags |= _cabi.FLAG_INVERT if invert else 0
+            else:
+                if invert:
+                    mask = np.invert(mask)
+                m = img_as_float32(mask) if mask.dtype != np.float32 else mask  # cl.py:205-206
+                if self.log:
+                    m = np.log(EPS + m)  # cl.py:207-208
+                arr, code = np.asarray(m, dtype=np.float32), _cabi.MASK_F32
+        return np.ascontiguousarray(arr), code, flags, lut
+
+    # -- processing ------------------------------------------------------------------------
+    def process_view(self, intrinsics, rot, tvec, mask):
+        """Process a new view (cl.py:190-227).
+
+        Parameters
+        ----------
+        intrinsics: list
+            [f_x, f_y, c_x, c_y]
+        rot: list of list
+            rotation matrix of the camera pose
+        tvec: list
+            translation vector of the camera pose
+        mask: numpy.ndarray
+            mask array (or float array if type is averaging)
+        """
+        self._process_batch([(intrinsics, rot, tvec, mask)], invert=False)
+        return
+
+    def process_views(self, views, invert=False):
+        """Fused form: ``views`` is a sequence of ``(intrinsics, rot, tvec, mask)``; same result
+        as calling ``process_view`` on each in order."""
+        views = list(views)
+        for s in range(0, len(views), MAX_VIEWS_PER_CALL):
+            self._process_batch(views[s:s + MAX_VIEWS_PER_CALL], invert)
+
+    def _process_batch(self, views, invert):
+        if not views:
+            return
+        n = len(views)
+        cams = np.empty((n, 16), dtype=np.float32)
+        hw = np.empty((n, 2), dtype=np.int32)
+        ptrs = (ctypes.c_void_p * n)()
+        keep = []
+        code0 = flags0 = lut0 = None
+        groups = []  # consecutive views that share (dtype code, flags, lut) go in one call
+        start = 0
+        for q, (intr, rot, tvec, mask) in enumerate(views):
+            cams[q, 0:4] = np.asarray(intr, dtype=np.float32).reshape(4)
+            cams[q, 4:13] = np.asarray(rot, dtype=np.float32).reshape(9)
+            cams[q, 13:16] = np.asarray(tvec, dtype=np.float32).reshape(3)
+            arr, code, flags, lut = self._prepare(mask, invert)
+            if logger.isEnabledFor(logging.DEBUG):
+                logger.debug("mask max: %.2f" % (arr.max()))  # cl.py:214
+            keep.append(arr)
+            hw[q] = arr.shape
+            ptrs[q] = arr.ctypes.data
+            sig = (code, flags, id(lut))
+            if q == 0:
+                code0, flags0, lut0 = code, flags, lut
+                sig0 = sig
+            elif sig != sig0:
+                groups.append((start, q, code0, flags0, lut0))
+                start, code0, flags0, lut0, sig0 = q, code, flags, lut, sig
+        groups.append((start, n, code0, flags0, lut0))
+        L = _cabi.lib()
+        for (a, b, code, flags, lut) in groups:
+            lut_p = lut.ctypes.data_as(_F) if lut is not None else None
+            sub_ptrs = (ctypes.c_void_p * (b - a))(*ptrs[a:b])
+            _cabi.check(L.bp_process_views(self._handle(), b - a, cams[a:b].ctypes.data_as(_F), sub_ptrs,
+                                           hw[a:b].ctypes.data_as(_I), code, flags, lut_p))
+
+    def get_values(self):
+        """Gets computed values from the device (cl.py:229-232)."""
+        out = self.values_h
+        _cabi.check(_cabi.lib().bp_get_values(self._handle(), out.ctypes.data_as(ctypes.c_void_p)))
+        return out.reshape(self.local_shape)
+
+    get_volume = get_values  # the name BASELINE.json's north_star uses
+
+    def process_fileset(self, fs, camera_metadata, invert=False):
+        """Processes a whole fileset (cl.py:234-257).
+
+        Parameters
+        ----------
+        fs : plantdb.db.Fileset or list of plantdb.db.File
+            The images `Fileset` or list of images `File` to process.
+        camera_metadata : str
+            Name of the metadata to use to get the camera intrinsics (fx, fy, cx, cy) & poses.
+        invert : bool, optional
+            If ``True``, invert the values of the mask file to process.
+        """
+        if self.labels is not None:
+            result = np.zeros((len(self.labels), *self.local_shape))
+            for i, label in enumerate(self.labels):
+                logger.info(f"Processing label '{label}'...")
+                if i != 0:
+                    self.clear()
+                result[i, :] = self.process_label(fs, camera_metadata, label, invert)
+            return result
+        else:
+            return self.process_label(fs, camera_metadata, None, invert=invert)
+
+    def process_label(self, fs, camera_metadata, label=None, invert=False):
+        """Processes a whole fileset for given label (cl.py:259-305).
+
+        Returns
+        -------
+        numpy.ndarray
+            The processed volume, for given label, if any.
+        """
+        if hasattr(fs, "get_files"):
+            fs = fs.get_files()
+
+        batch = []
+        for fi in fs:
+            # Skip file if not of the right label (when defined)
+            if label is not None and fi.get_metadata("channel") != label:
+                continue
+            logger.debug("processing file %s" % fi.id)
+            cam = fi.get_metadata(camera_metadata, default=None)
+            if cam is None:
+                logger.warning(f"Could not get camera params from '{camera_metadata}' for {fi.id}, skipping...")
+                continue
+            intrinsics = np.array(cam["camera_model"]['params'][0:4], dtype=np.float32)
+            rot = np.array(sum(cam['rotmat'], []), dtype=np.float32)
+            tvec = np.array(cam['tvec'], dtype=np.float32)
+            mask = _read_image(fi)
+            batch.append((intrinsics, rot, tvec, mask))
+            if len(batch) == MAX_VIEWS_PER_CALL:
+                self._process_batch(batch, invert)
+                batch = []
+        self._process_batch(batch, invert)
+        return self.get_values()
+
+    def clear(self):
+        """Re-seed the device grid with ``default_value`` (cl.py:307-311)."""
+        _cabi.check(_cabi.lib().bp_clear(self._handle()))
+        return
+
+    # -- extras used by parallel.py / bench.py ------------------------------------------------
+    def sync(self):
+        _cabi.check(_cabi.lib().bp_sync(self._handle()))
+
+    def timing(self):
+        """(kernel_ms, ingest_ms, launches): device time since the last call, launches since creation."""
+        k, g, n = ctypes.c_float(), ctypes.c_float(), ctypes.c_int64()
+        _cabi.check(_cabi.lib().bp_timing(self._handle(), ctypes.byref(k), ctypes.byref(g), ctypes.byref(n)))
+        return k.value, g.value, n.value
+
+    def device_state(self):
+        """(device pointer, bytes, nz pitch) of the raw state (see bp_device_state)."""
+        p, nb, pitch = ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_int32()
+        _cabi.check(_cabi.lib().bp_device_state(self._handle(), ctypes.byref(p), ctypes.byref(nb),
+                                                ctypes.byref(pitch)))
+        return p.value, nb.value, pitch.value
+
+
+def _read_image(fi):
+    """``plantdb.io.read_image`` (io.py:343-378) for a plantdb ``File`` when plantdb is
+    installed, else for the duck-typed files of ``fsdb_lite`` (``read_image()`` / ``path()``)."""
+    if hasattr(fi, "read_image"):
+        return fi.read_image()
+    try:
+        from plantdb import io
+        return io.read_image(fi)
+    except ImportError:
+        from PIL import Image
+        path = fi.path() if callable(getattr(fi, "path", None)) else fi
+        return np.asarray(Image.open(path))
