@@ -1,0 +1,412 @@
+#!/usr/bin/env python3
+"""bench.py — voxel-views/s of the back-projection hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload C5|C2|C4] [--scale S] [--mode carving|averaging]
+
+Default workload (N=1 and N>1): C5 of BASELINE.md §3 — carving a 1024^3 grid from 240 views of
+6000x4000 masks (the configuration north_star's target is quoted on; 1 GiB of int8 state + 5.8 GB
+of masks fit one B200).  With N ranks the grid is cut into N axis-0 slabs, every
+rank processes all views for its slab, no collective on the data path: total work is fixed
+("scaling": "strong").
+
+One step = clear the grid + ingest (bit-pack) every mask + the fused carve kernel over all views.
+  value : whole-job voxel-views/s with the uint8 masks already resident in HBM, device-timed
+  e2e   : same step through the public Backprojection API from pinned HOST masks, including the
+          H2D copies and the get_values() D2H of the int32 volume, wall-clock between syncs
+  roofline / cpu_baseline / clocks / gpu_launches : see DESIGN.md §Measurement
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "voxel-views/sec"
+UNIT = "voxel-views/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C5", choices=["C5", "C2", "C4"])
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink grid and images (debug only)")
+    ap.add_argument("--mode", default="carving", choices=["carving", "averaging"])
+    ap.add_argument("--cpu-planes", type=int, default=0, help="planes in the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(mode):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(mode)
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, c[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def sample_planes(nx, n):
+    """Evenly spread axis-0 planes used as the bounded CPU sample."""
+    n = max(1, min(n, nx))
+    return sorted({int((q + 0.5) * nx / n) for q in range(n)})
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py executes oracle/)
+# ---------------------------------------------------------------------------------------------
+def cpu_leg(w, masks_np, mode, planes, kind, gpu_planes=None):
+    """Time the CPU implementation on `planes` (each run as a 1-plane slab, all views).
+    kind == "port": oracle/bp_oracle.c restatement (global plane index, comparable bit for bit);
+    kind == "reference": the reference's own kernel source from oracle/_ref (origin shifted to the
+    plane), including the int32 widening process_view does per view (cl.py:215)."""
+    import ctypes
+    from oracle import backprojection_oracle as bo
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cams = w["cams"].astype(np.float32)
+    ny, nz = w["shape"][1], w["shape"][2]
+    n_views = len(cams)
+    F = ctypes.POINTER(ctypes.c_float)
+    I = ctypes.POINTER(ctypes.c_int32)
+    B = ctypes.POINTER(ctypes.c_uint8)
+    origin = np.array(w["origin"], dtype=np.float32)
+    vs = np.float32(w["voxel_size"])
+    shape1 = np.array([1, ny, nz], dtype=np.int32)
+    lut = None
+    if mode == "averaging":
+        lut = np.ascontiguousarray(bo.img_as_float32(np.arange(256, dtype=np.uint8)), dtype=np.float32)
+    lib = bo._lib("restatement" if kind == "port" else "ref_off")
+    ok = True
+    t_total = 0.0
+    for pi, i0 in enumerate(planes):
+        if mode == "carving":
+            state = np.zeros((1, ny, nz), dtype=np.int32)
+        else:
+            state = np.zeros((1, ny, nz), dtype=np.float32)
+        t0 = time.perf_counter()
+        for v in range(n_views):
+            m = masks_np[v]
+            H, W = m.shape
+            c = cams[v]
+            if kind == "port":
+                if mode == "carving":
+                    lib.oracle_carve_view(m.ctypes.data_as(B), H, W, state.ctypes.data_as(I), c[0:4].ctypes.data_as(F),
+                                          c[4:13].ctypes.data_as(F), c[13:16].ctypes.data_as(F),
+                                          origin.ctypes.data_as(F), ctypes.c_float(float(vs)),
+                                          shape1.ctypes.data_as(I), int(i0))
+                else:
+                    lib.oracle_average_view_lut(m.ctypes.data_as(B), lut.ctypes.data_as(F), H, W,
+                                                state.ctypes.data_as(F), c[0:4].ctypes.data_as(F),
+                                                c[4:13].ctypes.data_as(F), c[13:16].ctypes.data_as(F),
+                                                origin.ctypes.data_as(F), ctypes.c_float(float(vs)),
+                                                shape1.ctypes.data_as(I), int(i0))
+            else:
+                volinfo = np.array([origin[0] + np.float32(i0) * vs, origin[1], origin[2], vs], dtype=np.float32)
+                if mode == "carving":
+                    mh = np.ascontiguousarray(m, dtype=np.int32)  # cl.py:215
+                    lib.ref_carve_view(mh.ctypes.data_as(I), H, W, state.ctypes.data_as(I), c[0:4].ctypes.data_as(F),
+                                       c[4:13].ctypes.data_as(F), c[13:16].ctypes.data_as(F),
+                                       volinfo.ctypes.data_as(F), shape1.ctypes.data_as(I))
+                else:
+                    mh = np.ascontiguousarray(bo.img_as_float32(m), dtype=np.float32)  # cl.py:205-215
+                    lib.ref_average_view(mh.ctypes.data_as(F), H, W, state.ctypes.data_as(F),
+                                         c[0:4].ctypes.data_as(F), c[4:13].ctypes.data_as(F),
+                                         c[13:16].ctypes.data_as(F), volinfo.ctypes.data_as(F),
+                                         shape1.ctypes.data_as(I))
+        t_total += time.perf_counter() - t0
+        if gpu_planes is not None and kind == "port":
+            ok = ok and bool(np.array_equal(state[0], gpu_planes[pi]))
+    vv = float(len(planes)) * ny * nz * n_views
+    return vv / t_total, t_total, cores, ok
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from plant3dvision_b200 import synth
+    from oracle import backprojection_oracle as bo
+    import torch
+    w = synth.workload(args.workload, args.scale)
+    kind = "reference" if bo.have_backend("ref_off") else "port"
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    masks = render_all(w, dev, args.mode, pinned=False)
+    n_pl = args.cpu_planes or auto_planes(w, args.mode)
+    planes = sample_planes(w["shape"][0], n_pl)
+    for _ in range(min(args.warmup, 1)):
+        cpu_leg(w, masks, args.mode, planes[:1], kind)
+    times, vals = [], []
+    for _ in range(args.steps):
+        v, t, cores, _ = cpu_leg(w, masks, args.mode, planes, kind)
+        vals.append(v)
+        times.append(t)
+    value = float(len(planes)) * w["shape"][1] * w["shape"][2] * len(w["cams"]) * len(times) / sum(times)
+    sample = (f"{len(planes)} of {w['shape'][0]} axis-0 planes (evenly spread) x all {len(w['cams'])} views, "
+              f"per step; OpenMP over {cores} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32 projection, i32 state" if args.mode == "carving" else "f32", "data": "synthetic",
+        "config": workload_config(w, args, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def auto_planes(w, mode):
+    # ~10-30 s of CPU work: carving skips carved voxels early, averaging touches every voxel-view
+    per_plane = w["shape"][1] * w["shape"][2] * len(w["cams"])
+    budget = 6e9 if mode == "carving" else 1.5e9
+    return int(max(1, min(16, budget // max(per_plane, 1))))
+
+
+def workload_config(w, args, n_gpus):
+    return {
+        "workload": f"{w['name']} {args.mode}: grid {w['shape'][0]}x{w['shape'][1]}x{w['shape'][2]}, "
+                    f"{len(w['cams'])} views of {w['W']}x{w['H']} uint8 masks (synthetic phantom silhouettes)",
+        "grid": w["shape"], "views": len(w["cams"]), "mask_hw": [w["H"], w["W"]], "mode": args.mode,
+        "sharding": f"axis-0 slabs x{n_gpus}" if n_gpus > 1 else "single GPU",
+        "l2": "inputs larger than L2 (masks + grid >> 126 MB); grid re-seeded every step",
+        "scale": args.scale,
+    }
+
+
+def render_all(w, dev, mode, pinned):
+    """uint8 masks [n, H, W] in host memory (numpy); pinned when they feed the e2e leg."""
+    import torch
+    from plant3dvision_b200 import synth
+    n, H, W = len(w["cams"]), w["H"], w["W"]
+    host = torch.empty((n, H, W), dtype=torch.uint8, pin_memory=(pinned and torch.cuda.is_available()))
+    chunk = 16
+    soft = 2.0 if mode == "averaging" else 0.0
+    for a in range(0, n, chunk):
+        b = min(n, a + chunk)
+        host[a:b].copy_(synth.render_masks(w["cams"][a:b], w["capsules"], H, W, device=dev, soft_px=soft))
+    return host.numpy()
+
+
+# ---------------------------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from plant3dvision_b200 import synth
+    from plant3dvision_b200.cl import Backprojection
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    w = synth.workload(args.workload, args.scale)
+    nx, ny, nz = w["shape"]
+    n_views = len(w["cams"])
+    H, W = w["H"], w["W"]
+    i0, i1 = rank * nx // world, (rank + 1) * nx // world
+    cams = w["cams"].astype(np.float32)
+
+    # ---- inputs: rendered once, kept (a) pinned on the host for e2e, (b) resident in HBM for `value`
+    masks_np = render_all(w, dev, args.mode, pinned=True)
+    masks_d = torch.from_numpy(masks_np).to(dev)
+    ptrs = [masks_d[v].data_ptr() for v in range(n_views)]
+    hw = np.tile(np.array([[H, W]], dtype=np.int32), (n_views, 1))
+    views_host = [(cams[v, 0:4], cams[v, 4:13], cams[v, 13:16], masks_np[v]) for v in range(n_views)]
+
+    bp = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=args.mode, log=False, device=local,
+                        i_range=(i0, i1))
+    ext = torch.cuda.ExternalStream(bp.stream(), device=dev)
+
+    def step_resident():
+        bp.clear()
+        bp.process_device_views(cams, ptrs, hw)
+
+    def barrier():
+        bp.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    barrier()
+    bp.timing()  # reset the library's event accumulators
+    _, _, launches0 = bp.timing()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(args.steps):
+        step_resident()
+    e1.record(ext)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clk = clocks.stop() if rank == 0 else None
+    kernel_ms, ingest_ms, launches1 = bp.timing()
+    t = torch.tensor([ms_total, kernel_ms, ingest_ms, float(launches1 - launches0)], dtype=torch.float64, device=dev)
+    tmax, tsum = t.clone(), t.clone()
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    ms_step = float(tmax[0]) / args.steps
+    total_vv = float(nx) * ny * nz * n_views
+    value = total_vv / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (carve / average), SURVEY §8(d) algorithmic bytes
+    peak, peak_src = peaks()
+    bytes_per_vv = 4.0 if args.mode == "carving" else 8.0
+    mask_bytes = n_views * (H * W / 8.0 if args.mode == "carving" else float(H * W))
+    algo_bytes = bytes_per_vv * float(i1 - i0) * ny * nz * n_views + mask_bytes
+    k_ms = float(tmax[1]) / args.steps  # one launch per step (n_views <= 256)
+    n_launch_per_step = (n_views + 255) // 256
+    achieved = algo_bytes / (k_ms / n_launch_per_step * 1e-3) / 1e9 / n_launch_per_step
+    fused_floor = (1.0 if args.mode == "carving" else 8.0) * float(i1 - i0) * ny * nz + mask_bytes
+    roofline = {
+        "bound": "hbm", "kernel": "carve_kernel" if args.mode == "carving" else "average_kernel<u8>",
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": ncu_traffic(args.mode), "peak_source": peak_src,
+        "kernel_ms_per_launch": k_ms / n_launch_per_step, "ingest_ms_per_step": float(tmax[2]) / args.steps,
+        "algorithmic_bytes_per_launch": algo_bytes,
+        "note": "algorithmic bytes = SURVEY 8(d) per-view streaming traffic (4 B/voxel-view carving, 8 B averaging, "
+                "+ packed masks); the fused kernel keeps voxel state in registers across views, so HBM traffic is "
+                "far below it (see traffic) and frac may exceed 1: the kernel is FP32-issue / L1-gather bound, "
+                "see DESIGN.md",
+        "fused_floor_bytes_per_launch": fused_floor,
+    }
+
+    # ---- e2e: public API, pinned host masks, H2D + kernels + D2H of the int32 / float32 volume
+    e2e = None
+    if not args.no_e2e:
+        def step_e2e():
+            bp.clear()
+            bp.process_views(views_host)
+            return bp.get_values()
+        for _ in range(2):
+            vol = step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            vol = step_e2e()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": total_vv * args.steps / float(dt[0]), "unit": UNIT,
+               "h2d_bytes_per_step": int(n_views * H * W) * world,
+               "d2h_bytes_per_step": int(nx * ny * nz * 4), "ms_per_step": 1e3 * float(dt[0]) / args.steps}
+    else:
+        step_resident()
+        vol = bp.get_values()
+
+    # ---- CPU baseline (rank 0, N=1 only): oracle restatement on a bounded sample, also used as a checker
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        n_pl = args.cpu_planes or auto_planes(w, args.mode)
+        planes = sample_planes(nx, n_pl)
+        gpu_planes = [np.array(vol[p - i0]) for p in planes]
+        v, t, cores, ok = cpu_leg(w, masks_np, args.mode, planes, "port", gpu_planes)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{len(planes)} of {nx} axis-0 planes (evenly spread) x all {n_views} views, {t:.1f} s; "
+                         f"oracle/bp_oracle.c, OpenMP over {cores} threads",
+               "sample_matches_gpu": ok}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 projection, i8 state" if args.mode == "carving" else "f32",
+            "data": "synthetic", "config": workload_config(w, args, world),
+            "e2e": e2e, "gpu_launches": int(tsum[3]), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    bp.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

@@ -16,7 +16,7 @@ FLAG_INVERT, FLAG_BOOL_INVERT, FLAG_DEVICE_MASKS = 1, 2, 4
 # every symbol include/bp_b200.h declares; tests check the library exports all of them
 SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
-    "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_timing",
+    "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version",
 ]
 
@@ -50,6 +50,7 @@ def lib():
         L.bp_get_values_device.argtypes = [vp, vp]
         L.bp_device_state.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_int64), c_i]
         L.bp_sync.argtypes = [vp]
+        L.bp_stream.argtypes = [vp, ctypes.POINTER(vp)]
         L.bp_timing.argtypes = [vp, c_f, c_f, ctypes.POINTER(ctypes.c_int64)]
         L.bp_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.bp_host_free.argtypes = [vp]

@@ -301,6 +301,31 @@ class Backprojection(object):
             _cabi.check(L.bp_process_views(self._handle(), b - a, cams[a:b].ctypes.data_as(_F), sub_ptrs,
                                            hw[a:b].ctypes.data_as(_I), code, flags, lut_p))
 
+    def process_device_views(self, cams, mask_ptrs, hw, invert=False, dtype="uint8"):
+        """Fused pass over views whose masks already sit in device memory (inputs resident in HBM):
+        ``cams`` float32 ``[n, 16]`` (fx fy cx cy | rot | tvec), ``mask_ptrs`` n device addresses of
+        row-major ``H x W`` arrays of ``dtype`` ('uint8' or 'float32'), ``hw`` int ``[n, 2]``."""
+        n = len(mask_ptrs)
+        cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(n, 16)
+        hw = np.ascontiguousarray(hw, dtype=np.int32).reshape(n, 2)
+        if dtype == "uint8":
+            code, flags = _cabi.MASK_U8, (_cabi.FLAG_INVERT if invert else 0)
+            lut = self._lut("u8") if self._mode == _cabi.MODE_AVERAGING else None
+        elif dtype == "float32":
+            if invert:
+                raise TypeError("invert is not defined for float masks")
+            code, flags, lut = _cabi.MASK_F32, 0, None
+        else:
+            raise TypeError(f"Unsupported device mask dtype {dtype}")
+        flags |= _cabi.FLAG_DEVICE_MASKS
+        L = _cabi.lib()
+        for a in range(0, n, MAX_VIEWS_PER_CALL):
+            b = min(n, a + MAX_VIEWS_PER_CALL)
+            ptrs = (ctypes.c_void_p * (b - a))(*[int(p) for p in mask_ptrs[a:b]])
+            _cabi.check(L.bp_process_views(self._handle(), b - a, cams[a:b].ctypes.data_as(_F), ptrs,
+                                           hw[a:b].ctypes.data_as(_I), code, flags,
+                                           lut.ctypes.data_as(_F) if lut is not None else None))
+
     def get_values(self):
         """Gets computed values from the device (cl.py:229-232)."""
         out = self.values_h
@@ -372,6 +397,12 @@ class Backprojection(object):
     # -- extras used by parallel.py / bench.py ------------------------------------------------
     def sync(self):
         _cabi.check(_cabi.lib().bp_sync(self._handle()))
+
+    def stream(self):
+        """The handle's cudaStream_t as an int (for torch.cuda.ExternalStream)."""
+        p = ctypes.c_void_p()
+        _cabi.check(_cabi.lib().bp_stream(self._handle(), ctypes.byref(p)))
+        return p.value or 0
 
     def timing(self):
         """(kernel_ms, ingest_ms, launches): device time since the last call, launches since creation."""

@@ -1,0 +1,229 @@
+#!/usr/bin/env python3
+# -*- coding: utf-8 -*-
+"""
+plant3dvision_b200.tasks.cl
+___________________________
+
+``Voxels``: same parameters, defaults, bounding-box / shape / label resolution and outputs as the
+reference task (plant3dvision/tasks/cl.py:18-186), running on ``plant3dvision_b200.cl.Backprojection``.
+
+luigi / romitask / plantdb are not required: ``Voxels(scan, **params).run()`` and
+``run_voxels(scan_dir, config)`` work on a plain FSDB scan directory through ``fsdb_lite``.  The
+``[Voxels]`` section of the reference's TOML configs is accepted verbatim, including list / dict
+parameters given as JSON strings (e.g. ``labels = "[\\"background\\"]"``, configs/ml_pipe_real.toml:46)
+and the nested ``[Voxels.bounding_box]`` table (configs/geom_pipe_real.toml:36-39).
+"""
+import hashlib
+import json
+import logging
+import os
+import sys
+
+import numpy as np
+
+from .. import fsdb_lite
+
+logger = logging.getLogger(__name__)
+
+#: parameter defaults of the reference task (tasks/cl.py:79-91)
+DEFAULTS = dict(
+    upstream_mask="Masks",
+    upstream_colmap="Colmap",
+    query={},
+    camera_metadata="colmap_camera",
+    voxel_size=1.0,
+    type="carving",
+    log=True,
+    invert=False,
+    labels=[],
+    bounding_box=None,
+)
+
+
+def parse_params(section):
+    """``[Voxels]`` TOML section -> parameter dict with the reference's defaults.  luigi's config
+    ingestion hands list / dict parameters over as JSON strings; both forms are accepted."""
+    p = dict(DEFAULTS)
+    for k, v in dict(section or {}).items():
+        if k in ("query", "labels", "bounding_box") and isinstance(v, str):
+            v = json.loads(v)
+        p[k] = v
+    p["voxel_size"] = float(p["voxel_size"])
+    p["log"] = bool(p["log"])
+    p["invert"] = bool(p["invert"])
+    p["labels"] = list(p["labels"] or [])
+    p["query"] = dict(p["query"] or {})
+    if p["bounding_box"] is not None:
+        p["bounding_box"] = {a: list(p["bounding_box"][a]) for a in "xyz"}
+    return p
+
+
+def load_config(path):
+    """Read a pipeline TOML and return its ``[Voxels]`` parameters."""
+    try:
+        import tomllib
+    except ImportError:  # pragma: no cover
+        import tomli as tomllib
+    with open(path, "rb") as f:
+        cfg = tomllib.load(f)
+    return parse_params(cfg.get("Voxels", {}))
+
+
+def grid_from_bbox(bounding_box, voxel_size, displacement=None):
+    """Shape and origin of the voxel array (tasks/cl.py:127-147), in python floats like the task."""
+    x_min, x_max = bounding_box["x"]
+    y_min, y_max = bounding_box["y"]
+    z_min, z_max = bounding_box["z"]
+    if displacement is not None:
+        x_min += displacement["dx"]
+        x_max += displacement["dx"]
+        y_min += displacement["dy"]
+        y_max += displacement["dy"]
+        z_min += displacement["dz"]
+        z_max += displacement["dz"]
+    nx = int((x_max - x_min) / voxel_size) + 1
+    ny = int((y_max - y_min) / voxel_size) + 1
+    nz = int((z_max - z_min) / voxel_size) + 1
+    return [nx, ny, nz], [x_min, y_min, z_min]
+
+
+def _find_fileset(scan, task_name):
+    """The fileset an upstream task wrote: 'images' for ImagesFilesetExists, else the first
+    fileset named after the task (romitask names them ``<Task>_<params hash>``)."""
+    if task_name in ("ImagesFilesetExists", "images"):
+        return scan.get_fileset("images")
+    for fs in scan.get_filesets():
+        if fs.id == task_name or fs.id.startswith(task_name + "_"):
+            return fs
+    return None
+
+
+class Voxels:
+    """Computes a volume from backprojection of 2D segmented images.
+
+    Parameters are those of the reference task; ``scan`` is an ``fsdb_lite.Scan`` (or a path)."""
+
+    def __init__(self, scan, masks_fileset=None, **params):
+        self.scan = scan if hasattr(scan, "get_fileset") else fsdb_lite.Scan(scan)
+        unknown = set(params) - set(DEFAULTS)
+        if unknown:
+            raise TypeError(f"Unknown Voxels parameters: {sorted(unknown)}")
+        for k, v in parse_params(params).items():
+            setattr(self, k, v)
+        self._masks_fileset = masks_fileset
+
+    @property
+    def task_id(self):
+        sig = json.dumps({k: getattr(self, k) for k in DEFAULTS}, sort_keys=True, default=str)
+        return "Voxels_" + hashlib.md5(sig.encode()).hexdigest()[:10]
+
+    def resolve_bounding_box(self, masks_fileset):
+        """Precedence of tasks/cl.py:107-118: parameter, scan metadata, Colmap fileset, images fileset."""
+        bbox = self.bounding_box
+        if bbox is None:
+            bbox = self.scan.get_metadata("bounding_box")
+        if bbox is None and self.upstream_colmap == "Colmap":
+            colmap_fs = _find_fileset(self.scan, "Colmap")
+            if colmap_fs is not None:
+                bbox = colmap_fs.get_metadata("bounding_box")
+        if bbox is None:
+            images = self.scan.get_fileset("images")
+            if images is not None:
+                bbox = images.get_metadata("bounding_box")
+        return bbox
+
+    def compute(self, **bp_kwargs):
+        """Everything of ``run`` up to (not including) writing: returns (vol, labels, origin)."""
+        from ..cl import Backprojection
+        masks_fileset = self._masks_fileset or _find_fileset(self.scan, self.upstream_mask)
+        if masks_fileset is None:
+            raise IOError(f"No fileset found for upstream task '{self.upstream_mask}' in scan '{self.scan.id}'")
+        masks_files = masks_fileset.get_files(query=self.query)
+        logger.info(f"Processing a list of {len(masks_files)} mask files...")
+
+        bounding_box = self.resolve_bounding_box(masks_fileset)
+        if bounding_box is None:
+            logger.critical(f"Could not obtain valid bounding-box for {self.scan.id}!")
+            sys.exit("Error with bounding-box definition!")
+        logger.info(f"Bounding-box to use: {bounding_box}")
+
+        displacement = self.scan.get_metadata("displacement")
+        if displacement is None:
+            logger.warning("No 'displacement' found in scan metadata!")
+        shape, origin = grid_from_bbox(bounding_box, self.voxel_size, displacement)
+
+        if len(self.labels) == 0:
+            labels = masks_fileset.get_metadata("label_names", default=None)
+            if labels is None or len(labels) == 0:
+                logger.warning("No metadata 'label_names' in `masks_fileset`!")
+                labels = None
+        else:
+            labels = list(self.labels)
+
+        sc = Backprojection(shape=shape, origin=origin, voxel_size=float(self.voxel_size), type=str(self.type),
+                            labels=labels, log=bool(self.log), **bp_kwargs)
+        vol = sc.process_fileset(masks_files, str(self.camera_metadata), bool(self.invert))
+        if labels is None:
+            vol = vol.copy()  # detach from the pinned buffer before the device handle goes away
+        sc.close()
+        logger.debug(f"Voxel volume shape: {vol.shape}")
+        if vol.size and vol.min() == vol.max():  # tasks/cl.py:168 (np.unique) without the sort
+            logger.warning("There is something WRONG with the volume!")
+
+        # If conversion to log was requested, convert back applying `np.exp` (tasks/cl.py:172-174)
+        if self.log and self.type == "averaging":
+            vol = np.exp(vol)
+            vol[vol > 1] = 1.0
+        return vol, labels, origin
+
+    def run(self, **bp_kwargs):
+        """Run and write the output fileset: ``Voxels.npz`` (one array per label) or ``Voxels.tiff``
+        / ``Voxels.npy`` plus the file metadata ``{voxel_size, origin}`` (tasks/cl.py:176-186)."""
+        vol, labels, origin = self.compute(**bp_kwargs)
+        out_fs = self.scan.get_fileset(self.task_id, create=True)
+        if labels is not None:
+            f = out_fs.create_file("Voxels", "npz")
+            np.savez_compressed(f.path(), **{label: vol[i, :] for i, label in enumerate(labels)})
+        else:
+            f = out_fs.create_file("Voxels", "tiff")
+            write_volume(f.path(), vol)
+        f.set_metadata({'voxel_size': self.voxel_size, 'origin': [float(o) for o in origin]})
+        out_fs.set_metadata({"task_name": "Voxels", "task_params": {k: getattr(self, k) for k in DEFAULTS}})
+        return f
+
+
+def write_volume(path, vol):
+    """Multi-page TIFF, one page per axis-0 plane - the layout imageio gives plantdb's
+    ``io.write_volume`` (io.py:491-525).  Uses tifffile / imageio when present, else PIL."""
+    try:
+        import tifffile
+        tifffile.imwrite(path, vol)
+        return
+    except ImportError:
+        pass
+    from PIL import Image
+    pages = [Image.fromarray(np.ascontiguousarray(vol[i])) for i in range(vol.shape[0])]
+    pages[0].save(path, format="TIFF", save_all=True, append_images=pages[1:])
+
+
+def read_volume(path):
+    """Inverse of ``write_volume`` (plantdb io.read_volume)."""
+    try:
+        import tifffile
+        return tifffile.imread(path)
+    except ImportError:
+        pass
+    from PIL import Image, ImageSequence
+    with Image.open(path) as im:
+        return np.stack([np.asarray(p) for p in ImageSequence.Iterator(im)])
+
+
+def run_voxels(scan_dir, config=None, **overrides):
+    """``romi_run_task Voxels <scan_dir> --config <toml>`` without luigi: ``config`` is a TOML path
+    or an already parsed ``[Voxels]`` dict."""
+    if isinstance(config, (str, os.PathLike)):
+        params = load_config(config)
+    else:
+        params = parse_params(config)
+    params.update(overrides)
+    return Voxels(scan_dir, **params).run()
