@@ -418,6 +418,31 @@ class Backprojection(object):
         return p.value, nb.value, pitch.value
 
 
+    def state_tensor(self):
+        """torch tensor ALIASING the raw device state ``[planes, ny, nz_pitch]`` (int8 carving coding
+        0 carved < 1 seen < 2 unseen, or float32 partial sums): what ``parallel.py`` hands to NCCL."""
+        import torch
+        ptr, n_bytes, pitch = self.device_state()
+        carving = self._mode == _cabi.MODE_CARVING
+        shape = (self.local_shape[0], self.local_shape[1], pitch)
+
+        class _Span:  # minimal __cuda_array_interface__ exporter over memory owned by the handle
+            __cuda_array_interface__ = {"shape": shape, "typestr": "|i1" if carving else "<f4",
+                                        "data": (ptr or 0, False), "version": 2}
+
+        if ptr is None or n_bytes == 0:
+            return torch.empty(shape, dtype=torch.int8 if carving else torch.float32, device=f"cuda:{self.device}")
+        t = torch.as_tensor(_Span(), device=f"cuda:{self.device}")
+        t._bp_owner = self  # keep the handle alive as long as the alias is
+        return t
+
+    def adopt_state(self, state):
+        """Called after an in-place collective on ``state_tensor()`` ran on torch's current stream:
+        make the result visible to the handle's own stream."""
+        import torch
+        torch.cuda.current_stream(self.device).synchronize()
+
+
 def _read_image(fi):
     """``plantdb.io.read_image`` (io.py:343-378) for a plantdb ``File`` when plantdb is
     installed, else for the duck-typed files of ``fsdb_lite`` (``read_image()`` / ``path()``)."""

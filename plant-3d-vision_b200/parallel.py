@@ -1,0 +1,221 @@
+"""Multi-GPU back-projection: one process per GPU (``torchrun``), ``torch.distributed`` for the plumbing.
+
+The reference has no multi-device path (one OpenCL context, one queue).  Two ways to
+split the work of ``Backprojection.process_fileset`` (cl.py:234-305), both exact:
+
+``sharding="slabs"``  rank r holds planes ``[r*nx/G, (r+1)*nx/G)`` of axis 0 (contiguous in the C-order
+    layout, kernels/common.h:1-12) and processes EVERY view for them.  Voxels are independent, so
+    there is no collective on the data path; world points use the global plane index, so every slab
+    is bit-identical to the same planes of a single-GPU run.  ``get_values(gather=True)`` all-gathers.
+``sharding="views"``  every rank holds a full replica and processes views ``v = rank (mod G)``; the
+    replicas are then combined with ONE all-reduce of the raw device state:
+      carving    element-wise MIN over the int8 state 0 carved < 1 seen < 2 unseen.  The final
+                 state of a voxel is order-independent (carved if any view carves it, else seen if
+                 any view sees it, kernels/backprojection.c:65-83), which is exactly that MIN.
+                 (MIN over the reference's own {-1, 0, 1} coding would be wrong: min(0, 1) = 0.)
+      averaging  element-wise SUM of the float32 partial sums (ranks > 0 are seeded with 0 instead
+                 of ``default_value``).  The order of the float additions differs from the
+                 sequential view loop: equal within 1e-5 relative, not bit-identical.
+
+The engine that does the per-rank work is ``plant3dvision_b200.cl.Backprojection`` (CUDA); the
+class takes it as a parameter only so that the sharding logic can be exercised on CPU ranks (gloo)
+in the tests with a stand-in engine.
+"""
+import logging
+
+import numpy as np
+
+logger = logging.getLogger(__name__)
+
+CARVED, SEEN, UNSEEN = 0, 1, 2  # int8 device coding of the carving state (include/bp_b200.h)
+
+
+def slab_range(nx, rank, world):
+    """Planes ``[i0, i1)`` of axis 0 owned by ``rank``: contiguous, disjoint, covering ``[0, nx)``."""
+    return (rank * nx) // world, ((rank + 1) * nx) // world
+
+
+def partition_views(n_views, rank, world):
+    """Indices of the views ``rank`` processes under view sharding (round robin)."""
+    return list(range(rank, n_views, world))
+
+
+def encode_carve_state(vol, default_value=0):
+    """Reference coding (int32: -1 carved, 1 seen, ``default_value`` unseen; cl.py:173,
+    kernels/backprojection.c:79-83) -> monotone int8 coding.  Host-side twin of the device layout."""
+    vol = np.asarray(vol)
+    out = np.full(vol.shape, UNSEEN, dtype=np.int8)
+    out[vol == -1] = CARVED
+    if int(default_value) == 0:
+        out[vol == 1] = SEEN
+    return out
+
+
+def decode_carve_state(state, default_value=0):
+    """Inverse of ``encode_carve_state`` (what ``bp_get_values`` does on the device)."""
+    d = int(default_value)
+    state = np.asarray(state)
+    out = np.full(state.shape, d, dtype=np.int32)
+    if d == -1:
+        return out  # a grid seeded with -1 is inert (kernels/backprojection.c:65-67)
+    out[state == CARVED] = -1
+    out[state == SEEN] = 1 if d == 0 else d
+    return out
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+class DistributedBackprojection(object):
+    """``Backprojection`` over all ranks of a ``torch.distributed`` process group.
+
+    Same constructor and methods as ``plant3dvision_b200.cl.Backprojection``; every rank must make
+    the same calls with the same arguments (SPMD).  Extra keyword-only parameters:
+
+    sharding : {"slabs", "views"}
+    group : process group (default: the world group)
+    engine : class doing one rank's work (default ``plant3dvision_b200.cl.Backprojection``)
+    """
+
+    def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
+                 *, sharding="slabs", group=None, engine=None, **engine_kwargs):
+        if sharding not in ("slabs", "views"):
+            raise ValueError(f"Unknown sharding {sharding!r}, valid values are 'slabs' or 'views'!")
+        if type not in ("carving", "averaging"):
+            raise ValueError(f"Unknown kernel type {type}, valid values are 'averaging' or 'carving'!")
+        dist = _dist()
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.sharding = sharding
+        self.shape = [int(s) for s in shape]
+        self.origin = origin
+        self.voxel_size = voxel_size
+        self.type = type
+        self.default_value = default_value
+        self.labels = labels
+        self.log = log
+        self.dtype = np.int32 if type == "carving" else np.float32
+        if engine is None:
+            from .cl import Backprojection as engine
+        local_default = default_value
+        if sharding == "slabs":
+            self.i_range = slab_range(self.shape[0], self.rank, self.world)
+            engine_kwargs["i_range"] = self.i_range
+        else:
+            self.i_range = (0, self.shape[0])
+            if type == "averaging" and self.rank != 0:
+                local_default = 0  # the seed must enter the all-reduce SUM exactly once
+        self.local = engine(self.shape, origin, voxel_size, type=type, default_value=local_default, labels=labels,
+                            log=log, **engine_kwargs)
+        self._reduced = True  # nothing accumulated yet
+
+    # -- work distribution ---------------------------------------------------------------------
+    def my_views(self, n_views):
+        if self.sharding == "views":
+            return partition_views(n_views, self.rank, self.world)
+        return list(range(n_views))
+
+    def process_views(self, views, invert=False):
+        """``views``: the FULL sequence of ``(intrinsics, rot, tvec, mask)``, identical on every rank
+        (a rank only touches the masks of the views it owns)."""
+        views = list(views)
+        mine = [views[v] for v in self.my_views(len(views))]
+        self.local.process_views(mine, invert=invert)
+        self._reduced = False
+
+    def process_view(self, intrinsics, rot, tvec, mask):
+        """One view on every rank's grid part (slabs) / on the rank whose turn it is (views)."""
+        if self.sharding == "views":
+            turn = getattr(self, "_turn", 0)
+            self._turn = turn + 1
+            if turn % self.world != self.rank:
+                self._reduced = False
+                return
+        self.local.process_view(intrinsics, rot, tvec, mask)
+        self._reduced = False
+
+    def process_label(self, fs, camera_metadata, label=None, invert=False, gather=True):
+        """cl.py:259-305 distributed: the file loop (channel filter, camera lookup, warn + skip) runs
+        on every rank so that all agree on the view list; only owned views are decoded."""
+        if hasattr(fs, "get_files"):
+            fs = fs.get_files()
+        usable = []
+        for fi in fs:
+            if label is not None and fi.get_metadata("channel") != label:
+                continue
+            cam = fi.get_metadata(camera_metadata, default=None)
+            if cam is None:
+                logger.warning(f"Could not get camera params from '{camera_metadata}' for {fi.id}, skipping...")
+                continue
+            usable.append((fi, cam))
+        from .cl import _read_image
+        mine = []
+        for v in self.my_views(len(usable)):
+            fi, cam = usable[v]
+            intrinsics = np.array(cam["camera_model"]["params"][0:4], dtype=np.float32)
+            rot = np.array(sum(cam["rotmat"], []), dtype=np.float32)
+            tvec = np.array(cam["tvec"], dtype=np.float32)
+            mine.append((intrinsics, rot, tvec, _read_image(fi)))
+        self.local.process_views(mine, invert=invert)
+        self._reduced = False
+        return self.get_values(gather=gather)
+
+    def process_fileset(self, fs, camera_metadata, invert=False, gather=True):
+        """cl.py:234-257 distributed (float64 ``[L, ...]`` stack when labels are set)."""
+        if self.labels is not None:
+            result = None
+            for i, label in enumerate(self.labels):
+                if i != 0:
+                    self.clear()
+                vol = self.process_label(fs, camera_metadata, label, invert, gather=gather)
+                if result is None:
+                    result = np.zeros((len(self.labels), *vol.shape))
+                result[i, :] = vol
+            return result
+        return self.process_label(fs, camera_metadata, None, invert=invert, gather=gather)
+
+    # -- combination ---------------------------------------------------------------------------
+    def reduce(self):
+        """View sharding: all-reduce the raw state in place (MIN int8 / SUM float32).  Idempotent
+        until more views are processed.  Slab sharding: nothing to exchange."""
+        if self.sharding != "views" or self.world == 1 or self._reduced:
+            self._reduced = True
+            return
+        dist = _dist()
+        state = self.local.state_tensor()
+        self.local.sync()
+        op = dist.ReduceOp.MIN if self.type == "carving" else dist.ReduceOp.SUM
+        dist.all_reduce(state, op=op, group=self.group)
+        self.local.adopt_state(state)
+        self._reduced = True
+
+    def get_values(self, gather=True):
+        """The volume (cl.py:229-232).  Views: the full grid on every rank, after ``reduce()``.
+        Slabs: this rank's planes, or with ``gather`` the full grid all-gathered on every rank."""
+        self.reduce()
+        vol = self.local.get_values()
+        if self.sharding == "views" or self.world == 1 or not gather:
+            return vol
+        dist = _dist()
+        parts = [None] * self.world
+        dist.all_gather_object(parts, np.ascontiguousarray(vol), group=self.group)
+        return np.concatenate(parts, axis=0)
+
+    get_volume = get_values
+
+    def clear(self):
+        self.local.clear()
+        self._turn = 0
+        self._reduced = True
+
+    def close(self):
+        self.local.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

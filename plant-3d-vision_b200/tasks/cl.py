@@ -40,11 +40,16 @@ DEFAULTS = dict(
 )
 
 
-def parse_params(section):
+def parse_params(section, strict=True):
     """``[Voxels]`` TOML section -> parameter dict with the reference's defaults.  luigi's config
     ingestion hands list / dict parameters over as JSON strings; both forms are accepted."""
     p = dict(DEFAULTS)
     for k, v in dict(section or {}).items():
+        if k not in DEFAULTS and not strict:
+            # luigi's config ingestion ignores keys that are not parameters of the task
+            # (e.g. `use_colmap_poses` in configs/ml_pipe_real.toml:41)
+            logger.debug(f"Ignoring unknown [Voxels] key '{k}'")
+            continue
         if k in ("query", "labels", "bounding_box") and isinstance(v, str):
             v = json.loads(v)
         p[k] = v
@@ -66,7 +71,7 @@ def load_config(path):
         import tomli as tomllib
     with open(path, "rb") as f:
         cfg = tomllib.load(f)
-    return parse_params(cfg.get("Voxels", {}))
+    return parse_params(cfg.get("Voxels", {}), strict=False)
 
 
 def grid_from_bbox(bounding_box, voxel_size, displacement=None):
@@ -224,6 +229,6 @@ def run_voxels(scan_dir, config=None, **overrides):
     if isinstance(config, (str, os.PathLike)):
         params = load_config(config)
     else:
-        params = parse_params(config)
+        params = parse_params(config, strict=False)
     params.update(overrides)
     return Voxels(scan_dir, **params).run()

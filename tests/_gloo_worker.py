@@ -1,0 +1,100 @@
+"""Worker side of tests/test_parallel_gloo.py: CPU ranks (gloo) running the PRODUCT's sharding logic
+(plant3dvision_b200.parallel) over a stand-in engine backed by the CPU oracle.  Test infrastructure."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+class OracleEngine:
+    """Duck-types what ``DistributedBackprojection`` needs from ``cl.Backprojection``."""
+
+    def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
+                 i_range=None):
+        from oracle.backprojection_oracle import BackprojectionOracle
+        self.i_range = i_range or (0, shape[0])
+        self.default_value = default_value
+        self.type = type
+        local = [self.i_range[1] - self.i_range[0], shape[1], shape[2]]
+        self.o = BackprojectionOracle(local, origin, voxel_size, type=type, default_value=default_value,
+                                      labels=labels, log=log, i_offset=self.i_range[0])
+
+    def process_views(self, views, invert=False):
+        for (i, r, t, m) in views:
+            self.o.process_view(i, r, t, np.invert(m) if invert else m)
+
+    def process_view(self, i, r, t, m):
+        self.o.process_view(i, r, t, m)
+
+    def get_values(self):
+        return self.o.get_values()
+
+    def clear(self):
+        self.o.clear()
+
+    def close(self):
+        pass
+
+    def sync(self):
+        pass
+
+    def state_tensor(self):
+        import torch
+        from plant3dvision_b200.parallel import encode_carve_state
+        if self.type == "carving":
+            return torch.from_numpy(encode_carve_state(self.o.get_values(), self.default_value))
+        return torch.from_numpy(self.o.get_values())  # aliases the oracle's buffer
+
+    def adopt_state(self, state):
+        from plant3dvision_b200.parallel import decode_carve_state
+        if self.type == "carving":
+            self.o.values_h = decode_carve_state(state.numpy(), self.default_value)
+
+
+def scene(seed=5, n_views=7, H=120, W=160):
+    rng = np.random.default_rng(seed)
+    shape, vs, origin = [21, 17, 30], 1.5, [-15.0, -12.0, -20.0]
+    views = []
+    for v in range(n_views):
+        th = 2 * np.pi * v / n_views
+        C = np.array([90 * np.cos(th), 90 * np.sin(th), 10.0])
+        fwd = -C / np.linalg.norm(C)
+        right = np.cross(fwd, [0, 0, 1.0])
+        right /= np.linalg.norm(right)
+        R = np.stack([right, np.cross(fwd, right), fwd])
+        intr = np.array([150.0, 150.0, W / 2, H / 2], dtype=np.float32)
+        yy, xx = np.mgrid[0:H, 0:W]
+        blob = ((xx - W / 2) ** 2 / (30 + 5 * v) ** 2 + (yy - H / 2) ** 2 / 45 ** 2) < 1
+        mask = (blob * rng.integers(1, 256, (H, W))).astype(np.uint8)
+        views.append((intr, R.astype(np.float32).reshape(-1), (-R @ C).astype(np.float32), mask))
+    return shape, origin, vs, views
+
+
+def worker(rank, world, port, kind, sharding, default_value, out_dir):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from plant3dvision_b200.parallel import DistributedBackprojection
+        shape, origin, vs, views = scene()
+        bp = DistributedBackprojection(shape, origin, vs, type=kind, default_value=default_value, log=False,
+                                       sharding=sharding, engine=OracleEngine)
+        bp.process_views(views)
+        vol = bp.get_values(gather=True)
+        again = bp.get_values(gather=True)  # reduce() must be idempotent
+        assert np.array_equal(vol, again)
+        part = bp.get_values(gather=False)
+        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), vol=vol, part=part, i_range=np.array(bp.i_range))
+        bp.clear()
+        for v in views:  # per-view entry point, every rank calling it for every view
+            bp.process_view(*v)
+        assert np.array_equal(bp.get_values(gather=True), vol) or kind == "averaging"
+        if kind == "averaging":
+            np.testing.assert_allclose(bp.get_values(gather=True), vol, rtol=1e-5, atol=1e-6)
+    finally:
+        dist.destroy_process_group()

@@ -1,0 +1,106 @@
+"""CPU tests of the drop-in boundary: ``libbp_b200.so`` loads, exports every symbol that
+``include/bp_b200.h`` declares, rejects bad arguments with the documented codes, and FAILS LOUDLY
+(no CPU fallback) when there is no CUDA device.  No compute call is made here."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from plant3dvision_b200 import _cabi
+
+HEADER = os.path.join(ROOT, "include", "bp_b200.h")
+
+
+def declared_functions():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(bp_[a-z0-9_]+)\s*\(", text)))
+
+
+def have_cuda():
+    import torch
+    return torch.cuda.is_available()
+
+
+def test_header_declares_what_the_binding_lists():
+    assert declared_functions() == sorted(_cabi.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _cabi.lib()
+    for name in declared_functions():
+        assert hasattr(lib, name), f"libbp_b200.so does not export {name}"
+    # and nothing C++-mangled leaks an unintended bp_* entry point
+    assert lib.bp_version().decode().startswith("bp_b200 ")
+    assert lib.bp_version().decode().endswith("sm_100a")
+
+
+def test_header_cites_the_reference_interface_it_replaces():
+    text = open(HEADER).read()
+    for cite in ("cl.py:118-188", "cl.py:190-227", "cl.py:229-232", "cl.py:307-311",
+                 "kernels/backprojection.c:57-84", "kernels/backprojection.c:36-55"):
+        assert cite in text, cite
+
+
+def test_bad_arguments_are_rejected_with_codes_and_messages():
+    lib = _cabi.lib()
+    h = ctypes.c_void_p()
+    shape = (ctypes.c_int32 * 3)(4, 4, 4)
+    origin = (ctypes.c_float * 3)(0, 0, 0)
+    assert lib.bp_create(ctypes.byref(h), shape, 0, 4, origin, 1.0, 7, 0.0, 0) == -1  # BP_EINVAL: mode
+    assert b"mode" in lib.bp_last_error()
+    assert lib.bp_create(ctypes.byref(h), shape, 3, 2, origin, 1.0, 0, 0.0, 0) == -1  # bad slab
+    assert b"slab" in lib.bp_last_error()
+    neg = (ctypes.c_int32 * 3)(4, -1, 4)
+    assert lib.bp_create(ctypes.byref(h), neg, 0, 4, origin, 1.0, 0, 0.0, 0) == -1
+    assert lib.bp_create(None, shape, 0, 4, origin, 1.0, 0, 0.0, 0) == -1
+    for fn in (lib.bp_clear, lib.bp_sync):
+        assert fn(None) == -1
+    assert lib.bp_get_values(None, None) == -1
+    assert lib.bp_destroy(None) == 0  # like free(NULL)
+    assert lib.bp_host_free(None) == 0
+    with pytest.raises(ValueError):
+        _cabi.check(-1)
+    with pytest.raises(MemoryError):
+        _cabi.check(-3)
+    with pytest.raises(_cabi.BackprojectionError):
+        _cabi.check(-2)
+
+
+@pytest.mark.skipif(have_cuda(), reason="this checks the no-GPU behaviour")
+def test_no_cpu_fallback_without_a_cuda_device():
+    lib = _cabi.lib()
+    h = ctypes.c_void_p()
+    shape = (ctypes.c_int32 * 3)(4, 4, 4)
+    origin = (ctypes.c_float * 3)(0, 0, 0)
+    rc = lib.bp_create(ctypes.byref(h), shape, 0, 4, origin, 1.0, 0, 0.0, 0)
+    assert rc == -2 and not h.value  # BP_ECUDA, no handle
+    from plant3dvision_b200.cl import Backprojection
+    with pytest.raises(_cabi.BackprojectionError):
+        Backprojection([10, 10, 10], [0, 0, 0], 1.0)
+
+
+def test_missing_library_is_a_hard_error(monkeypatch, tmp_path):
+    monkeypatch.setattr(_cabi, "_lib", None)
+    monkeypatch.setattr(_cabi, "LIB_PATH", str(tmp_path / "libbp_b200.so"))
+    with pytest.raises(ImportError, match="no CPU fallback"):
+        _cabi.lib()
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "plant-3d-vision_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text and "libbp_oracle" not in text, f
+
+
+def test_unknown_type_raises_like_the_reference():
+    from plant3dvision_b200.cl import Backprojection
+    with pytest.raises(ValueError, match="Unknown kernel type"):
+        Backprojection([10, 10, 10], [0, 0, 0], 1.0, type="nope")  # cl.py:151-152
+    assert np.dtype(np.int32) == np.int32

@@ -1,0 +1,202 @@
+"""CPU tests of the host side that mirrors the reference interface: ``[Voxels]`` TOML parameters and
+defaults (tasks/cl.py:79-91), bounding-box -> shape/origin (tasks/cl.py:127-147), the FSDB reader, the
+mask conversions of cl.py:205-215 / 300-301 (which flags / tables are handed to the C ABI), and the
+volume writers.  Nothing here launches a kernel."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from plant3dvision_b200 import _cabi, fsdb_lite
+from plant3dvision_b200 import cl as bcl
+from plant3dvision_b200.tasks import cl as tcl
+
+# the [Voxels] sections of the reference's configs, verbatim (configs/geom_pipe_virtual.toml:1-8,
+# geom_pipe_real.toml:30-39, ml_pipe_real.toml:38-46, ml_pipe_virtual.toml:19-26)
+GEOM_VIRTUAL = '''
+[Voxels]
+upstream_mask = "ImagesFilesetExists"
+upstream_colmap = "DummyTask"
+query = "{\\"channel\\":\\"background\\"}"  # use the (inverted) background masks
+camera_metadata = "camera"
+voxel_size = 0.06  # ~9x smaller than real plants
+type = "carving"
+invert = true
+'''
+GEOM_REAL = '''
+[Voxels]
+upstream_mask = "Masks"
+upstream_colmap = "Colmap"
+camera_metadata = "colmap_camera"
+voxel_size = 0.5
+type = "carving"
+[Voxels.bounding_box]  # default to None
+x = [300, 450]
+y = [300, 450]
+z = [-175, 100]
+'''
+ML_REAL = '''
+[Voxels]
+upstream_mask = "Segmentation2D"
+upstream_colmap = "Colmap"
+use_colmap_poses = true
+voxel_size = 1
+type = "averaging"
+log = false # default to true
+invert = false
+labels = "[\\"background\\"]"
+'''
+ML_VIRTUAL = '''
+[Voxels]
+upstream_mask = "Segmentation2D"
+use_colmap_poses = false
+voxel_size = 0.3
+type = "averaging"
+log = false # default to true
+invert = false
+labels = "[\\"background\\", \\"fruit\\", \\"leaf\\", \\"pedicel\\", \\"stem\\"]"
+'''
+
+
+def cfg(tmp_path, text):
+    p = tmp_path / "pipe.toml"
+    p.write_text(text)
+    return tcl.load_config(str(p))
+
+
+def test_defaults_match_the_reference_task():
+    p = tcl.parse_params({})
+    assert p == dict(upstream_mask="Masks", upstream_colmap="Colmap", query={}, camera_metadata="colmap_camera",
+                     voxel_size=1.0, type="carving", log=True, invert=False, labels=[], bounding_box=None)
+
+
+def test_reference_configs_parse(tmp_path):
+    p = cfg(tmp_path, GEOM_VIRTUAL)
+    assert p["query"] == {"channel": "background"} and p["invert"] is True and p["camera_metadata"] == "camera"
+    assert p["voxel_size"] == 0.06 and p["type"] == "carving" and p["upstream_mask"] == "ImagesFilesetExists"
+    p = cfg(tmp_path, GEOM_REAL)
+    assert p["bounding_box"] == {"x": [300, 450], "y": [300, 450], "z": [-175, 100]} and p["voxel_size"] == 0.5
+    p = cfg(tmp_path, ML_REAL)  # unknown key `use_colmap_poses` is ignored, as luigi does
+    assert p["labels"] == ["background"] and p["log"] is False and p["type"] == "averaging" and p["voxel_size"] == 1.0
+    assert "use_colmap_poses" not in p
+    p = cfg(tmp_path, ML_VIRTUAL)
+    assert p["labels"] == ["background", "fruit", "leaf", "pedicel", "stem"]
+    with pytest.raises(TypeError):
+        tcl.Voxels("/nonexistent", use_colmap_poses=True)  # direct construction is strict
+
+
+def test_grid_from_bbox_known_shapes(vp_inputs):
+    # virtual_plant bbox at 0.06 -> [386, 397, 1998]; CI variant 0.1 -> [232, 239, 1199]
+    assert tcl.grid_from_bbox(vp_inputs["bbox"], 0.06)[0] == [386, 397, 1998]
+    assert tcl.grid_from_bbox(vp_inputs["bbox"], 0.1)[0] == [232, 239, 1199]
+    assert tcl.grid_from_bbox(vp_inputs["bbox"], 0.3)[0] == [78, 80, 400]
+    real = {"x": [300, 450], "y": [300, 450], "z": [-175, 100]}
+    assert tcl.grid_from_bbox(real, 0.5) == ([301, 301, 551], [300, 300, -175])
+    assert tcl.grid_from_bbox(real, 1.0)[0] == [151, 151, 276]
+    shape, origin = tcl.grid_from_bbox(real, 1.0, {"dx": 1.5, "dy": -2, "dz": 10})  # tasks/cl.py:127-140
+    assert shape == [151, 151, 276] and origin == [301.5, 298, -165]
+
+
+def make_scan(tmp_path, with_cam=True, n=3, channels=("background", "stem")):
+    from PIL import Image
+    scan = tmp_path / "scan_001"
+    (scan / "images").mkdir(parents=True)
+    (scan / "metadata" / "images").mkdir(parents=True)
+    files = []
+    rng = np.random.default_rng(0)
+    for v in range(n):
+        for ch in channels:
+            fid = f"{v:05d}_{ch}"
+            Image.fromarray((rng.random((12, 16)) < 0.5).astype(np.uint8) * 255).save(scan / "images" / f"{fid}.png")
+            md = {"channel": ch, "shot_id": f"{v:05d}"}
+            if with_cam and not (v == 1 and ch == "stem"):
+                md["camera"] = {"camera_model": {"params": [20.0, 20.0, 8.0, 6.0, 0, 0, 0, 0]},
+                                "rotmat": [[1, 0, 0], [0, 1, 0], [0, 0, 1]], "tvec": [0, 0, 30.0 + v]}
+            json.dump(md, open(scan / "metadata" / "images" / f"{fid}.json", "w"))
+            files.append({"id": fid, "file": f"{fid}.png"})
+    json.dump({"filesets": [{"id": "images", "files": files}]}, open(scan / "files.json", "w"))
+    json.dump({"bounding_box": {"x": [-4, 4], "y": [-3, 3], "z": [-2, 2]}, "label_names": list(channels)},
+              open(scan / "metadata" / "images.json", "w"))
+    json.dump({"displacement": {"dx": 0.0, "dy": 0.0, "dz": 0.0}}, open(scan / "metadata" / "metadata.json", "w"))
+    return scan
+
+
+def test_fsdb_lite_reads_the_on_disk_layout(tmp_path):
+    scan = fsdb_lite.Scan(make_scan(tmp_path))
+    fs = scan.get_fileset("images")
+    assert scan.id == "scan_001" and len(fs.get_files()) == 6
+    bg = fs.get_files(query={"channel": "background"})  # fsdb.py:2735-2791 filter
+    assert [f.id for f in bg] == ["00000_background", "00001_background", "00002_background"]
+    assert fs.get_metadata("bounding_box")["x"] == [-4, 4] and fs.get_metadata("nope", default=5) == 5
+    assert bg[0].get_metadata("camera")["tvec"] == [0, 0, 30.0]
+    assert fs.get_file("00001_stem").get_metadata("camera", default=None) is None
+    img = bg[0].read_image()
+    assert img.dtype == np.uint8 and img.shape == (12, 16)
+    out = scan.get_fileset("Voxels_x", create=True)
+    f = out.create_file("Voxels", "npz")
+    f.set_metadata({"voxel_size": 1.0, "origin": [0, 0, 0]})
+    again = fsdb_lite.Scan(scan.dir)
+    assert again.get_fileset("Voxels_x").get_file("Voxels").get_metadata("voxel_size") == 1.0
+
+
+def test_voxels_resolves_bbox_labels_and_task_id(tmp_path):
+    scan = make_scan(tmp_path)
+    t = tcl.Voxels(str(scan), upstream_mask="ImagesFilesetExists", upstream_colmap="DummyTask", camera_metadata="camera",
+                   query={"channel": "background"})
+    assert t.resolve_bounding_box(None) == {"x": [-4, 4], "y": [-3, 3], "z": [-2, 2]}  # images fileset md (:115-118)
+    t2 = tcl.Voxels(str(scan), bounding_box={"x": [0, 1], "y": [0, 1], "z": [0, 1]})
+    assert t2.resolve_bounding_box(None)["x"] == [0, 1]  # the parameter wins (:107-109)
+    assert t.task_id.startswith("Voxels_") and t.task_id != t2.task_id
+
+
+def bp_shell(mode, log=False):
+    """A Backprojection without a device handle: enough for the pure host conversions."""
+    bp = bcl.Backprojection.__new__(bcl.Backprojection)
+    bp._mode, bp.log, bp._lut_cache = mode, log, {}
+    return bp
+
+
+def test_img_as_float32_and_tables():
+    u8 = np.arange(256, dtype=np.uint8)
+    f = bcl.img_as_float32(u8)
+    assert f.dtype == np.float32 and f[0] == 0 and f[255] == 1 and f[51] == np.float32(51) * np.float32(1.0 / 255)  # float32 product, as skimage computes it
+    assert np.array_equal(bcl.img_as_float32(np.array([True, False])), np.array([1, 0], dtype=np.float32))
+    assert bcl.img_as_float32(np.array([65535], dtype=np.uint16))[0] == 1
+    bp = bp_shell(_cabi.MODE_AVERAGING, log=True)
+    lut = bp._lut("u8")
+    assert np.array_equal(lut, np.log(np.float32(1e-10) + f).astype(np.float32)) or np.allclose(lut, np.log(1e-10 + f))
+    assert lut.dtype == np.float32 and lut[0] == np.float32(np.log(np.float32(0) + 1e-10))
+    assert bp._lut("u8") is lut  # cached: process_views groups views by table identity
+
+
+@pytest.mark.parametrize("invert", [False, True])
+def test_prepare_chooses_dtype_flags_and_tables(invert):
+    carve, avg = bp_shell(_cabi.MODE_CARVING), bp_shell(_cabi.MODE_AVERAGING)
+    m8 = np.zeros((3, 4), dtype=np.uint8)
+    arr, code, flags, lut = carve._prepare(m8, invert)
+    assert (code, flags, lut) == (_cabi.MASK_U8, _cabi.FLAG_INVERT if invert else 0, None) and arr is m8
+    arr, code, flags, lut = carve._prepare(m8.astype(bool), invert)
+    assert (code, flags) == (_cabi.MASK_U8, _cabi.FLAG_BOOL_INVERT if invert else 0) and arr.dtype == np.uint8
+    arr, code, flags, lut = carve._prepare(np.full((3, 4), 7, dtype=np.int64), invert)
+    assert code == _cabi.MASK_I32 and flags == 0 and (arr == (~7 if invert else 7)).all()  # host np.invert
+    arr, code, flags, lut = avg._prepare(m8, invert)
+    assert code == _cabi.MASK_U8 and lut is not None and lut.shape == (256,)
+    arr, code, flags, lut = avg._prepare(np.full((3, 4), 65535, dtype=np.uint16), invert)
+    assert code == _cabi.MASK_F32 and lut is None and arr.dtype == np.float32 and (arr == (0 if invert else 1)).all()
+    if invert:
+        with pytest.raises(TypeError):
+            carve._prepare(np.zeros((3, 4), dtype=np.float32), True)  # np.invert on floats raises (cl.py:300-301)
+    with pytest.raises(ValueError):
+        carve._prepare(np.zeros((3, 4, 3), dtype=np.uint8), invert)
+
+
+def test_volume_writers_round_trip(tmp_path):
+    vol = (np.arange(4 * 5 * 6).reshape(4, 5, 6) % 3 - 1).astype(np.int32)
+    p = str(tmp_path / "v.tiff")
+    tcl.write_volume(p, vol)
+    back = tcl.read_volume(p)
+    assert back.shape == vol.shape and np.array_equal(back, vol)
+    volf = np.linspace(0, 1, 4 * 5 * 6, dtype=np.float32).reshape(4, 5, 6)
+    tcl.write_volume(p, volf)
+    assert np.array_equal(tcl.read_volume(p), volf)
