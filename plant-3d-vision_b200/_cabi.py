@@ -17,7 +17,7 @@ FLAG_INVERT, FLAG_BOOL_INVERT, FLAG_DEVICE_MASKS = 1, 2, 4
 SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
     "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
-    "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version",
+    "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
 ]
 
 _lib = None
@@ -52,6 +52,8 @@ def lib():
         L.bp_sync.argtypes = [vp]
         L.bp_stream.argtypes = [vp, ctypes.POINTER(vp)]
         L.bp_timing.argtypes = [vp, c_f, c_f, ctypes.POINTER(ctypes.c_int64)]
+        L.bp_selftest_division.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64,
+                                           ctypes.POINTER(ctypes.c_uint64)]
         L.bp_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.bp_host_free.argtypes = [vp]
         L.bp_last_error.restype = ctypes.c_char_p

@@ -74,18 +74,25 @@ def scene(seed=5, n_views=7, H=120, W=160):
     return shape, origin, vs, views
 
 
-def worker(rank, world, port, kind, sharding, default_value, out_dir):
+def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="gloo"):
+    import torch
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    engine_kwargs = {"engine": OracleEngine}
+    if backend == "nccl":  # the real thing: one GPU per rank, CUDA engine, NCCL all-reduce of device state
+        torch.cuda.set_device(rank)
+        engine_kwargs = {"device": rank}
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from plant3dvision_b200.parallel import DistributedBackprojection
         shape, origin, vs, views = scene()
         bp = DistributedBackprojection(shape, origin, vs, type=kind, default_value=default_value, log=False,
-                                       sharding=sharding, engine=OracleEngine)
+                                       sharding=sharding, **engine_kwargs)
         bp.process_views(views)
-        vol = bp.get_values(gather=True)
+        vol = np.array(bp.get_values(gather=True))  # copy: get_values aliases a reused host buffer
         again = bp.get_values(gather=True)  # reduce() must be idempotent
         assert np.array_equal(vol, again)
         part = bp.get_values(gather=False)
