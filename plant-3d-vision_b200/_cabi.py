@@ -20,6 +20,15 @@ SYMBOLS = [
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
 ]
 
+# every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
+V2P_SYMBOLS = [
+    "bp_vol2pcd", "bp_vol2pcd_info", "bp_vol2pcd_fetch", "bp_vol2pcd_device", "bp_vol2pcd_signed_distance",
+    "bp_vol2pcd_free", "bp_multiclass_select", "bp_device_free",
+]
+V2P_U8, V2P_I8, V2P_I32, V2P_F32, V2P_F64 = 0, 1, 2, 3, 4
+V2P_BIN_GT, V2P_BIN_EQ, V2P_BIN_GE = 0, 1, 2
+V2P_FLAG_DEVICE_VOLUME = 1
+
 _lib = None
 
 
@@ -56,6 +65,22 @@ def lib():
                                            ctypes.POINTER(ctypes.c_uint64)]
         L.bp_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.bp_host_free.argtypes = [vp]
+        c_d = ctypes.POINTER(ctypes.c_double)
+        c_l = ctypes.POINTER(ctypes.c_int64)
+        L.bp_vol2pcd.argtypes = [ctypes.POINTER(vp), ctypes.c_int, vp, ctypes.c_int, ctypes.c_uint32, c_i,
+                                 ctypes.c_int64, ctypes.c_int, ctypes.c_double, c_d, ctypes.c_double,
+                                 ctypes.c_double, ctypes.c_double, ctypes.c_double, c_d, ctypes.c_int]
+        L.bp_vol2pcd_info.argtypes = [vp, c_l, c_f, c_f, c_l, c_l]
+        L.bp_vol2pcd_fetch.argtypes = [vp, vp, vp]
+        L.bp_vol2pcd_device.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp)]
+        L.bp_vol2pcd_signed_distance.argtypes = [vp, vp, c_d]
+        L.bp_vol2pcd_free.argtypes = [vp]
+        L.bp_multiclass_select.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int,
+                                           ctypes.c_uint32, c_i, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                           ctypes.c_double, ctypes.c_int, ctypes.POINTER(vp)]
+        L.bp_device_free.argtypes = [ctypes.c_int, vp]
+        for name in V2P_SYMBOLS:
+            getattr(L, name).restype = ctypes.c_int
         L.bp_last_error.restype = ctypes.c_char_p
         L.bp_version.restype = ctypes.c_char_p
         for name in SYMBOLS:

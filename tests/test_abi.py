@@ -14,8 +14,11 @@ from plant3dvision_b200 import _cabi
 HEADER = os.path.join(ROOT, "include", "bp_b200.h")
 
 
-def declared_functions():
-    text = open(HEADER).read()
+V2P_HEADER = os.path.join(ROOT, "include", "vol2pcd_b200.h")
+
+
+def declared_functions(header=HEADER):
+    text = open(header).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(bp_[a-z0-9_]+)\s*\(", text)))
 
@@ -29,9 +32,20 @@ def test_header_declares_what_the_binding_lists():
     assert declared_functions() == sorted(_cabi.SYMBOLS)
 
 
+def test_vol2pcd_header_matches_binding_and_cites_the_reference():
+    assert declared_functions(V2P_HEADER) == sorted(_cabi.V2P_SYMBOLS)
+    text = open(V2P_HEADER).read()
+    for cite in ("proc3d.py:490-570", "tasks/proc3d.py:80-115"):
+        assert cite in text, cite
+    lib = _cabi.lib()
+    assert lib.bp_vol2pcd_free(None) == 0
+    assert lib.bp_vol2pcd_info(None, None, None, None, None, None) == -1
+    assert lib.bp_vol2pcd(None, 0, None, 0, 0, None, 0, 0, 0.5, None, 1.0, 0.0, 0.0, 0.0, None, 4) == -1
+
+
 def test_library_exports_every_declared_symbol():
     lib = _cabi.lib()
-    for name in declared_functions():
+    for name in declared_functions() + declared_functions(V2P_HEADER):
         assert hasattr(lib, name), f"libbp_b200.so does not export {name}"
     # and nothing C++-mangled leaks an unintended bp_* entry point
     assert lib.bp_version().decode().startswith("bp_b200 ")
