@@ -165,10 +165,13 @@ def test_handoff_from_live_averaging_handle(vp_inputs, log):
     vs = 0.6
     shape, origin = vp_shape_origin(vp_inputs["bbox"], vs)
     bp = Backprojection(shape, origin, vs, type="averaging", log=log)
-    maps = vp_inputs["maps"]["stem"]
-    views = [(*split_cam(vp_inputs["cams"][v]), maps[v]) for v in range(4 if not log else 2)]
-    bp.process_views(views)
+    # log: product of per-view probabilities, so use the (inverted) background channel = plant silhouette,
+    # which reaches 1.0; plain averaging: a few views of a thin organ's probability map
+    maps = vp_inputs["maps"]["background" if log else "stem"]
+    views = [(*split_cam(vp_inputs["cams"][v]), maps[v]) for v in range(0, 18, 3 if log else 5)]
+    bp.process_views(views, invert=log)
     vol = bp.get_values().copy()
+    assert 0 < (np.exp(vol) > 0.5 if log else vol > 0.5).sum() < vol.size
     got = proc3d.vol2pcd(bp, np.asarray(origin, dtype=np.float64), vs, 0, return_distance=True)
     bp.close()
     ref_vol = vol
