@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--cpu-planes", type=int, default=0, help="planes in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-averaging", action="store_true", help="carving run: skip the secondary averaging leg")
     return ap.parse_args()
 
 
@@ -268,40 +269,16 @@ def render_all(w, dev, mode, pinned):
     return host.numpy()
 
 
-# ---------------------------------------------------------------------------------------------
-# the B200 arm
-# ---------------------------------------------------------------------------------------------
-def run_b200(args):
+def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, rank, local, dev, with_cpu=True):
+    """Device-resident throughput, roofline, e2e and CPU sample of one mode on the already rendered masks."""
     import torch
     import torch.distributed as dist
-    from plant3dvision_b200 import synth
     from plant3dvision_b200.cl import Backprojection
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device - the B200 arm has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    dev = torch.device("cuda", local)
-
-    w = synth.workload(args.workload, args.scale)
     nx, ny, nz = w["shape"]
     n_views = len(w["cams"])
     H, W = w["H"], w["W"]
     i0, i1 = rank * nx // world, (rank + 1) * nx // world
-    cams = w["cams"].astype(np.float32)
-
-    # ---- inputs: rendered once, kept (a) pinned on the host for e2e, (b) resident in HBM for `value`
-    masks_np = render_all(w, dev, args.mode, pinned=True)
-    masks_d = torch.from_numpy(masks_np).to(dev)
-    ptrs = [masks_d[v].data_ptr() for v in range(n_views)]
-    hw = np.tile(np.array([[H, W]], dtype=np.int32), (n_views, 1))
-    views_host = [(cams[v, 0:4], cams[v, 4:13], cams[v, 13:16], masks_np[v]) for v in range(n_views)]
-
-    bp = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=args.mode, log=False, device=local,
+    bp = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False, device=local,
                         i_range=(i0, i1))
     ext = torch.cuda.ExternalStream(bp.stream(), device=dev)
 
@@ -344,17 +321,17 @@ def run_b200(args):
 
     # ---- roofline of the dominant kernel (carve / average), SURVEY §8(d) algorithmic bytes
     peak, peak_src = peaks()
-    bytes_per_vv = 4.0 if args.mode == "carving" else 8.0
-    mask_bytes = n_views * (H * W / 8.0 if args.mode == "carving" else float(H * W))
+    bytes_per_vv = 4.0 if mode == "carving" else 8.0
+    mask_bytes = n_views * (H * W / 8.0 if mode == "carving" else float(H * W))
     algo_bytes = bytes_per_vv * float(i1 - i0) * ny * nz * n_views + mask_bytes
     k_ms = float(tmax[1]) / args.steps  # one launch per step (n_views <= 256)
     n_launch_per_step = (n_views + 255) // 256
     achieved = algo_bytes / (k_ms / n_launch_per_step * 1e-3) / 1e9 / n_launch_per_step
-    fused_floor = (1.0 if args.mode == "carving" else 8.0) * float(i1 - i0) * ny * nz + mask_bytes
+    fused_floor = (1.0 if mode == "carving" else 8.0) * float(i1 - i0) * ny * nz + mask_bytes
     roofline = {
-        "bound": "hbm", "kernel": "carve_kernel" if args.mode == "carving" else "average_kernel<u8>",
+        "bound": "hbm", "kernel": "carve_kernel" if mode == "carving" else "average_kernel<u8>",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": ncu_traffic(args.mode), "peak_source": peak_src,
+        "traffic": ncu_traffic(mode), "peak_source": peak_src,
         "kernel_ms_per_launch": k_ms / n_launch_per_step, "ingest_ms_per_step": float(tmax[2]) / args.steps,
         "algorithmic_bytes_per_launch": algo_bytes,
         "note": "algorithmic bytes = SURVEY 8(d) per-view streaming traffic (4 B/voxel-view carving, 8 B averaging, "
@@ -390,26 +367,78 @@ def run_b200(args):
 
     # ---- CPU baseline (rank 0, N=1 only): oracle restatement on a bounded sample, also used as a checker
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        n_pl = args.cpu_planes or auto_planes(w, args.mode)
+    if rank == 0 and world == 1 and not args.no_cpu and with_cpu:
+        n_pl = args.cpu_planes or auto_planes(w, mode)
         planes = sample_planes(nx, n_pl)
         gpu_planes = [np.array(vol[p - i0]) for p in planes]
-        v, t, cores, ok = cpu_leg(w, masks_np, args.mode, planes, "port", gpu_planes)
+        v, t, cores, ok = cpu_leg(w, masks_np, mode, planes, "port", gpu_planes)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{len(planes)} of {nx} axis-0 planes (evenly spread) x all {n_views} views, {t:.1f} s; "
                          f"oracle/bp_oracle.c, OpenMP over {cores} threads",
                "sample_matches_gpu": ok}
 
+    bp.close()
+    return {"value": value, "ms_per_step": ms_step, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+            "gpu_launches": int(tsum[3]), "clocks": clk}
+
+
+# ---------------------------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from plant3dvision_b200 import synth
+    from plant3dvision_b200.cl import Backprojection
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    w = synth.workload(args.workload, args.scale)
+    nx, ny, nz = w["shape"]
+    n_views = len(w["cams"])
+    H, W = w["H"], w["W"]
+    i0, i1 = rank * nx // world, (rank + 1) * nx // world
+    cams = w["cams"].astype(np.float32)
+
+    # ---- inputs: rendered once, kept (a) pinned on the host for e2e, (b) resident in HBM for `value`
+    masks_np = render_all(w, dev, args.mode, pinned=True)
+    masks_d = torch.from_numpy(masks_np).to(dev)
+    ptrs = [masks_d[v].data_ptr() for v in range(n_views)]
+    hw = np.tile(np.array([[H, W]], dtype=np.int32), (n_views, 1))
+    views_host = [(cams[v, 0:4], cams[v, 4:13], cams[v, 13:16], masks_np[v]) for v in range(n_views)]
+
+    m = measure_mode(args, args.mode, w, cams, masks_np, ptrs, hw, views_host, world, rank, local, dev)
+    # BASELINE.json's metric covers both kernels: the default (carving) run also measures averaging on the
+    # same views (the 0/255 masks read as probability maps 0.0 / 1.0), reported under "averaging"
+    other = None
+    if args.mode == "carving" and not args.no_averaging:
+        a = measure_mode(args, "averaging", w, cams, masks_np, ptrs, hw, views_host, world, rank, local, dev)
+        other = {"metric": METRIC, "value": a["value"], "unit": UNIT, "ms_per_step": a["ms_per_step"], "dtype": "f32",
+                 "e2e": a["e2e"], "roofline": a["roofline"], "cpu_baseline": a["cpu_baseline"],
+                 "gpu_launches": a["gpu_launches"],
+                 "workload": "same grid and views, type='averaging', log=False, uint8 maps"}
+    value, ms_step, roofline, e2e, cpu, clk = (m["value"], m["ms_per_step"], m["roofline"], m["e2e"],
+                                               m["cpu_baseline"], m["clocks"])
+    launches_total = m["gpu_launches"] + (other["gpu_launches"] if other else 0)
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32 projection, i8 state" if args.mode == "carving" else "f32",
             "data": "synthetic", "config": workload_config(w, args, world),
-            "e2e": e2e, "gpu_launches": int(tsum[3]), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": e2e, "gpu_launches": launches_total, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
         }
+        if other is not None:
+            line["averaging"] = other
         print(json.dumps(line), flush=True)
-    bp.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
