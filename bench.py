@@ -249,7 +249,8 @@ def workload_config(w, args, n_gpus):
         "workload": f"{w['name']} {args.mode}: grid {w['shape'][0]}x{w['shape'][1]}x{w['shape'][2]}, "
                     f"{len(w['cams'])} views of {w['W']}x{w['H']} uint8 masks (synthetic phantom silhouettes)",
         "grid": w["shape"], "views": len(w["cams"]), "mask_hw": [w["H"], w["W"]], "mode": args.mode,
-        "sharding": f"axis-0 slabs x{n_gpus}" if n_gpus > 1 else "single GPU",
+        "sharding": (f"axis-0 slabs x{n_gpus}; masks ingested 1/{n_gpus} per rank + all-gather of the packed tiles "
+                     f"over NVLink (NCCL)") if n_gpus > 1 else "single GPU",
         "l2": "inputs larger than L2 (masks + grid >> 126 MB); grid re-seeded every step",
         "scale": args.scale,
     }
@@ -278,16 +279,24 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
     n_views = len(w["cams"])
     H, W = w["H"], w["W"]
     i0, i1 = rank * nx // world, (rank + 1) * nx // world
-    bp = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False, device=local,
-                        i_range=(i0, i1))
-    ext = torch.cuda.ExternalStream(bp.stream(), device=dev)
+    if world > 1:
+        # axis-0 slabs; mask ingest sharded over the ranks + one all-gather over NVLink (parallel.py)
+        from plant3dvision_b200.parallel import DistributedBackprojection
+        bp = DistributedBackprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False,
+                                       sharding="slabs", device=local)
+        eng = bp.local
+        assert tuple(bp.i_range) == (i0, i1)
+    else:
+        bp = eng = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False, device=local,
+                                  i_range=(i0, i1))
+    ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
 
     def step_resident():
         bp.clear()
         bp.process_device_views(cams, ptrs, hw)
 
     def barrier():
-        bp.sync()
+        eng.sync()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -296,8 +305,8 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
     for _ in range(max(args.warmup, 3)):
         step_resident()
     barrier()
-    bp.timing()  # reset the library's event accumulators
-    _, _, launches0 = bp.timing()
+    eng.timing()  # reset the library's event accumulators
+    _, _, launches0 = eng.timing()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -309,7 +318,7 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
     barrier()
     ms_total = e0.elapsed_time(e1)
     clk = clocks.stop() if rank == 0 else None
-    kernel_ms, ingest_ms, launches1 = bp.timing()
+    kernel_ms, ingest_ms, launches1 = eng.timing()
     t = torch.tensor([ms_total, kernel_ms, ingest_ms, float(launches1 - launches0)], dtype=torch.float64, device=dev)
     tmax, tsum = t.clone(), t.clone()
     if world > 1:
@@ -347,7 +356,7 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         def step_e2e():
             bp.clear()
             bp.process_views(views_host)
-            return bp.get_values()
+            return bp.get_values(gather=False) if world > 1 else bp.get_values()
         for _ in range(2):
             vol = step_e2e()
         barrier()
@@ -359,11 +368,11 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": total_vv * args.steps / float(dt[0]), "unit": UNIT,
-               "h2d_bytes_per_step": int(n_views * H * W) * world,
+               "h2d_bytes_per_step": int(n_views * H * W),  # N > 1: every mask crosses PCIe once (sharded ingest)
                "d2h_bytes_per_step": int(nx * ny * nz * 4), "ms_per_step": 1e3 * float(dt[0]) / args.steps}
     else:
         step_resident()
-        vol = bp.get_values()
+        vol = bp.get_values(gather=False) if world > 1 else bp.get_values()
 
     # ---- CPU baseline (rank 0, N=1 only): oracle restatement on a bounded sample, also used as a checker
     cpu = None
@@ -445,5 +454,10 @@ def run_b200(args):
 
 
 if __name__ == "__main__":
+    # stdout carries exactly ONE JSON line: native libraries that print to file descriptor 1 (NCCL's version banner)
+    # are pointed at stderr, Python's own sys.stdout keeps the original descriptor
+    _out = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_out, "w")
     a = parse_args()
     sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

@@ -326,6 +326,54 @@ class Backprojection(object):
                                            hw[a:b].ctypes.data_as(_I), code, flags,
                                            lut.ctypes.data_as(_F) if lut is not None else None))
 
+    # -- sharded ingest (multi-GPU slab mode, see parallel.py) ------------------------------------
+    @staticmethod
+    def packed_size(H, W):
+        """Bytes one ``H x W`` mask packs to (32x32-pixel bit tiles)."""
+        n = ctypes.c_int64()
+        _cabi.check(_cabi.lib().bp_packed_size(int(H), int(W), ctypes.byref(n)))
+        return n.value
+
+    def pack_views(self, masks, dst_ptr, view_stride, invert=False, device_masks=False, hw=None):
+        """Upload + bit-pack ``masks`` (2-D uint8 / bool arrays, or with ``device_masks`` device addresses of
+        uint8 arrays whose sizes are ``hw``) to ``dst_ptr + q * view_stride`` in device memory.  Carving only."""
+        n = len(masks)
+        if n == 0:
+            return
+        ptrs = (ctypes.c_void_p * n)()
+        keep = []
+        if device_masks:
+            hw = np.ascontiguousarray(hw, dtype=np.int32).reshape(n, 2)
+            for q in range(n):
+                ptrs[q] = int(masks[q])
+            code, flags = _cabi.MASK_U8, (_cabi.FLAG_INVERT if invert else 0) | _cabi.FLAG_DEVICE_MASKS
+        else:
+            hw = np.empty((n, 2), dtype=np.int32)
+            code = flags = None
+            for q, m in enumerate(masks):
+                arr, c, f, _ = self._prepare(m, invert)
+                if code is None:
+                    code, flags = c, f
+                elif (c, f) != (code, flags):
+                    raise TypeError("pack_views needs masks of one dtype")
+                keep.append(arr)
+                hw[q] = arr.shape
+                ptrs[q] = arr.ctypes.data
+        _cabi.check(_cabi.lib().bp_pack_views(self._handle(), n, ptrs, hw.ctypes.data_as(_I), code, flags,
+                                              ctypes.c_void_p(int(dst_ptr)), int(view_stride)))
+
+    def process_packed_views(self, cams, packed_ptrs, hw):
+        """Fused carve over views whose bit tiles (``pack_views`` layout) already sit in device memory."""
+        n = len(packed_ptrs)
+        cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(n, 16)
+        hw = np.ascontiguousarray(hw, dtype=np.int32).reshape(n, 2)
+        L = _cabi.lib()
+        for a in range(0, n, MAX_VIEWS_PER_CALL):
+            b = min(n, a + MAX_VIEWS_PER_CALL)
+            ptrs = (ctypes.c_void_p * (b - a))(*[int(p) for p in packed_ptrs[a:b]])
+            _cabi.check(L.bp_process_views(self._handle(), b - a, cams[a:b].ctypes.data_as(_F), ptrs,
+                                           hw[a:b].ctypes.data_as(_I), _cabi.MASK_U8, _cabi.FLAG_PACKED_MASKS, None))
+
     def get_values(self):
         """Gets computed values from the device (cl.py:229-232)."""
         out = self.values_h

@@ -80,7 +80,7 @@ class DistributedBackprojection(object):
     """
 
     def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
-                 *, sharding="slabs", group=None, engine=None, **engine_kwargs):
+                 *, sharding="slabs", group=None, engine=None, ingest="auto", **engine_kwargs):
         if sharding not in ("slabs", "views"):
             raise ValueError(f"Unknown sharding {sharding!r}, valid values are 'slabs' or 'views'!")
         if type not in ("carving", "averaging"):
@@ -111,6 +111,14 @@ class DistributedBackprojection(object):
         self.local = engine(self.shape, origin, voxel_size, type=type, default_value=local_default, labels=labels,
                             log=log, **engine_kwargs)
         self._reduced = True  # nothing accumulated yet
+        if ingest not in ("auto", "sharded", "replicated"):
+            raise ValueError(f"Unknown ingest {ingest!r}")
+        # slab sharding needs every mask on every rank.  "sharded": a rank uploads (PCIe) and bit-packs only
+        # the views v = rank (mod G) and the ranks exchange the results with ONE all-gather over NVLink
+        # (carving: 1 bit per pixel; averaging: the uint8 maps) instead of G copies of every mask crossing
+        # PCIe.  "replicated": every rank ingests every mask itself (what happens on CPU test engines).
+        self.ingest = ingest
+        self._xbuf = None
 
     # -- work distribution ---------------------------------------------------------------------
     def my_views(self, n_views):
@@ -118,10 +126,112 @@ class DistributedBackprojection(object):
             return partition_views(n_views, self.rank, self.world)
         return list(range(n_views))
 
+    # -- sharded ingest (slabs) ----------------------------------------------------------------
+    def _can_shard_ingest(self, shapes, dtypes):
+        if self.sharding != "slabs" or self.world == 1 or self.ingest == "replicated":
+            return False
+        ok = (hasattr(self.local, "pack_views") and len(set(shapes)) == 1 and
+              all(np.dtype(d) == np.uint8 for d in dtypes))
+        if ok and self.ingest == "auto" and self.type == "averaging" and self.world < 4:
+            # measured at G = 2 (profiles/r01_bench_n2_*.json): the averaging kernel hides a full upload per rank
+            # (225 ms replicated vs 250 ms sharded); the exchange pays off once PCIe time exceeds kernel time / G
+            return False
+        if not ok and self.ingest == "sharded":
+            raise ValueError("sharded ingest needs a CUDA engine and uint8 masks of one size")
+        return ok
+
+    #: raw mask bytes per pipeline chunk of the sharded ingest
+    CHUNK_BYTES = 512 << 20
+
+    def _exchange_buffers(self, n_per, stride):
+        import torch
+        want = (self.world, n_per, stride)
+        if self._xbuf is None or tuple(self._xbuf[0].shape) != want:
+            self._xbuf = [torch.empty(want, dtype=torch.uint8, device=f"cuda:{self.local.device}") for _ in range(2)]
+        return self._xbuf
+
+    def _process_views_sharded(self, cams, masks, H, W, invert):
+        """Slab mode, host masks (all ``H x W`` uint8): chunk c of the views is uploaded 1/G per rank (carving:
+        and bit-packed), all-gathered over NVLink and carved / averaged, while chunk c+1 is being uploaded —
+        two exchange buffers, ordering by CUDA events between torch's stream (copies, NCCL) and the engine's
+        stream (pack, carve / average); no host synchronisation inside the loop.  Chunks are contiguous view
+        ranges in the caller's order, so the averaging sums keep the sequential view order (bit-identical)."""
+        import torch
+        dist = _dist()
+        n, G, r = len(masks), self.world, self.rank
+        carving = self.type == "carving"
+        stride = self.local.packed_size(H, W) if carving else ((H * W + 255) // 256) * 256
+        # carving: one chunk per 256 views (the pack + carve of a chunk sweeps the slab once, and there is no
+        # compute worth hiding the upload behind); averaging: ~CHUNK_BYTES of maps, upload hidden behind the kernel
+        per_chunk = 256 if carving else max(1, self.CHUNK_BYTES // (H * W))
+        per_chunk = min(n, max(G, (per_chunk // G) * G))  # a multiple of G, at most n
+        n_per = (per_chunk + G - 1) // G
+        bufs = self._exchange_buffers(n_per, stride)
+        dev = bufs[0].device
+        cur = torch.cuda.current_stream(dev)
+        eng = torch.cuda.ExternalStream(self.local.stream(), device=dev)
+        hw = np.tile(np.array([[H, W]], dtype=np.int32), (per_chunk, 1))
+        done = [None, None]  # event after the pass that last read each buffer
+        for ci, c0 in enumerate(range(0, n, per_chunk)):
+            c1 = min(n, c0 + per_chunk)
+            buf = bufs[ci & 1]
+            mine = list(range(c0 + r, c1, G))
+            if done[ci & 1] is not None:
+                cur.wait_event(done[ci & 1])      # NCCL / copies must not overwrite what a pass still reads
+            if carving:
+                # (the engine's own stream is already ordered behind that pass)
+                self.local.pack_views([masks[v] for v in mine], buf[r].data_ptr(), stride, invert=invert)
+                ev = torch.cuda.Event()
+                ev.record(eng)
+                cur.wait_event(ev)
+            else:
+                for q, v in enumerate(mine):
+                    buf[r, q, :H * W].view(H, W).copy_(torch.from_numpy(np.ascontiguousarray(masks[v])),
+                                                       non_blocking=True)
+            dist.all_gather_into_tensor(buf.view(-1), buf[r].reshape(-1), group=self.group)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            eng.wait_event(ev)
+            base = buf.data_ptr()
+            ptrs = [base + (((v - c0) % G) * n_per + (v - c0) // G) * stride for v in range(c0, c1)]
+            if carving:
+                self.local.process_packed_views(cams[c0:c1], ptrs, hw[:c1 - c0])
+            else:
+                self.local.process_device_views(cams[c0:c1], ptrs, hw[:c1 - c0], invert=invert)
+            done[ci & 1] = torch.cuda.Event()
+            done[ci & 1].record(eng)
+        for ev in done:                            # host masks are not retained past the call
+            if ev is not None:
+                ev.synchronize()
+
+    def process_device_views(self, cams, mask_ptrs, hw, invert=False):
+        """Masks resident in HBM on every rank (device addresses of uint8 / float32 arrays): nothing to exchange,
+        every rank ingests from its own copy (packing 1/G each and all-gathering the tiles was measured slower
+        than packing everything locally at 3.7 TB/s: profiles/r01_bench_n2_*.json)."""
+        if self.sharding == "views":
+            mine = self.my_views(len(mask_ptrs))
+            cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(-1, 16)[mine]
+            hw = np.ascontiguousarray(hw, dtype=np.int32).reshape(-1, 2)[mine]
+            mask_ptrs = [mask_ptrs[v] for v in mine]
+        if len(mask_ptrs):
+            self.local.process_device_views(cams, mask_ptrs, hw, invert=invert)
+        self._reduced = False
+
     def process_views(self, views, invert=False):
         """``views``: the FULL sequence of ``(intrinsics, rot, tvec, mask)``, identical on every rank
         (a rank only touches the masks of the views it owns)."""
         views = list(views)
+        if views and self._can_shard_ingest([np.shape(v[3]) for v in views], [np.asarray(v[3]).dtype for v in views]):
+            n = len(views)
+            cams = np.empty((n, 16), dtype=np.float32)
+            for q, (intr, rot, tvec, _) in enumerate(views):
+                cams[q, 0:4] = np.asarray(intr, dtype=np.float32).reshape(4)
+                cams[q, 4:13] = np.asarray(rot, dtype=np.float32).reshape(9)
+                cams[q, 13:16] = np.asarray(tvec, dtype=np.float32).reshape(3)
+            H, W = np.shape(views[0][3])
+            self._process_views_sharded(cams, [v[3] for v in views], int(H), int(W), invert)
+            self._reduced = False
+            return
         mine = [views[v] for v in self.my_views(len(views))]
         self.local.process_views(mine, invert=invert)
         self._reduced = False

@@ -89,6 +89,8 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
     try:
         from plant3dvision_b200.parallel import DistributedBackprojection
         shape, origin, vs, views = scene()
+        if backend == "nccl" and sharding == "slabs":
+            engine_kwargs["ingest"] = "sharded"  # exercise the NVLink exchange for both kernels at world size 2
         bp = DistributedBackprojection(shape, origin, vs, type=kind, default_value=default_value, log=False,
                                        sharding=sharding, **engine_kwargs)
         bp.process_views(views)
@@ -103,5 +105,26 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
         assert np.array_equal(bp.get_values(gather=True), vol) or kind == "averaging"
         if kind == "averaging":
             np.testing.assert_allclose(bp.get_values(gather=True), vol, rtol=1e-5, atol=1e-6)
+        if backend == "nccl" and sharding == "slabs":
+            # masks resident in HBM on every rank (bench.py's `value` leg): sharded pack + all-gather of bit tiles
+            bp.clear()
+            dev = [torch.from_numpy(v[3]).cuda(rank) for v in views]
+            cams = np.stack([np.concatenate([np.ravel(v[0]), np.ravel(v[1]), np.ravel(v[2])]) for v in views])
+            hw = np.array([m.shape for m in dev], dtype=np.int32)
+            bp.process_device_views(cams.astype(np.float32), [m.data_ptr() for m in dev], hw)
+            assert np.array_equal(bp.get_values(gather=True), vol)
+            # the chunked pipeline of the sharded ingest (2 views per chunk -> 4 chunks, both exchange buffers reused)
+            bp.clear()
+            type(bp).CHUNK_BYTES = 3 * views[0][3].size
+            bp._xbuf = None
+            bp.process_views(views)
+            assert np.array_equal(bp.get_values(gather=True), vol)
+            # and the inverted form against the host-side inversion
+            bp.clear()
+            bp.process_views(views, invert=True)
+            a = np.array(bp.get_values(gather=True))
+            bp.clear()
+            bp.process_views([(i, r, t, np.invert(m)) for (i, r, t, m) in views])
+            assert np.array_equal(bp.get_values(gather=True), a)
     finally:
         dist.destroy_process_group()
