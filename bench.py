@@ -368,7 +368,9 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": total_vv * args.steps / float(dt[0]), "unit": UNIT,
-               "h2d_bytes_per_step": int(n_views * H * W),  # N > 1: every mask crosses PCIe once (sharded ingest)
+               # sharded ingest: every mask crosses PCIe once; replicated: once per rank
+               "h2d_bytes_per_step": int(n_views * H * W) * (world if getattr(bp, "last_ingest", None) == "replicated" else 1),
+               "ingest": getattr(bp, "last_ingest", None) or "single GPU",
                "d2h_bytes_per_step": int(nx * ny * nz * 4), "ms_per_step": 1e3 * float(dt[0]) / args.steps}
     else:
         step_resident()

@@ -119,6 +119,7 @@ class DistributedBackprojection(object):
         # PCIe.  "replicated": every rank ingests every mask itself (what happens on CPU test engines).
         self.ingest = ingest
         self._xbuf = None
+        self.last_ingest = None  # how the last process_views call moved the masks
 
     # -- work distribution ---------------------------------------------------------------------
     def my_views(self, n_views):
@@ -231,7 +232,9 @@ class DistributedBackprojection(object):
             H, W = np.shape(views[0][3])
             self._process_views_sharded(cams, [v[3] for v in views], int(H), int(W), invert)
             self._reduced = False
+            self.last_ingest = "sharded"
             return
+        self.last_ingest = "replicated"
         mine = [views[v] for v in self.my_views(len(views))]
         self.local.process_views(mine, invert=invert)
         self._reduced = False
