@@ -249,7 +249,7 @@ def workload_config(w, args, n_gpus):
         "workload": f"{w['name']} {args.mode}: grid {w['shape'][0]}x{w['shape'][1]}x{w['shape'][2]}, "
                     f"{len(w['cams'])} views of {w['W']}x{w['H']} uint8 masks (synthetic phantom silhouettes)",
         "grid": w["shape"], "views": len(w["cams"]), "mask_hw": [w["H"], w["W"]], "mode": args.mode,
-        "sharding": (f"axis-0 slabs x{n_gpus}; masks ingested 1/{n_gpus} per rank + all-gather of the packed tiles "
+        "sharding": (f"axis-0 stripes (blocks of 8 planes dealt round robin) x{n_gpus}; masks ingested 1/{n_gpus} per rank + all-gather of the packed tiles "
                      f"over NVLink (NCCL)") if n_gpus > 1 else "single GPU",
         "l2": "inputs larger than L2 (masks + grid >> 126 MB); grid re-seeded every step",
         "scale": args.scale,
@@ -283,9 +283,8 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         # axis-0 slabs; mask ingest sharded over the ranks + one all-gather over NVLink (parallel.py)
         from plant3dvision_b200.parallel import DistributedBackprojection
         bp = DistributedBackprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False,
-                                       sharding="slabs", device=local)
+                                       sharding="stripes", device=local)
         eng = bp.local
-        assert tuple(bp.i_range) == (i0, i1)
     else:
         bp = eng = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False, device=local,
                                   i_range=(i0, i1))
@@ -332,11 +331,12 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
     peak, peak_src = peaks()
     bytes_per_vv = 4.0 if mode == "carving" else 8.0
     mask_bytes = n_views * (H * W / 8.0 if mode == "carving" else float(H * W))
-    algo_bytes = bytes_per_vv * float(i1 - i0) * ny * nz * n_views + mask_bytes
+    n_local = len(eng.planes)  # axis-0 planes this rank holds
+    algo_bytes = bytes_per_vv * float(n_local) * ny * nz * n_views + mask_bytes
     k_ms = float(tmax[1]) / args.steps  # one launch per step (n_views <= 256)
     n_launch_per_step = (n_views + 255) // 256
     achieved = algo_bytes / (k_ms / n_launch_per_step * 1e-3) / 1e9 / n_launch_per_step
-    fused_floor = (1.0 if mode == "carving" else 8.0) * float(i1 - i0) * ny * nz + mask_bytes
+    fused_floor = (1.0 if mode == "carving" else 8.0) * float(n_local) * ny * nz + mask_bytes
     roofline = {
         "bound": "hbm", "kernel": "carve_kernel" if mode == "carving" else "average_kernel<u8>",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -18,7 +18,7 @@ SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
     "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
-    "bp_pack_views", "bp_packed_size",
+    "bp_pack_views", "bp_packed_size", "bp_create_striped",
 ]
 
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
@@ -50,6 +50,8 @@ def lib():
         vp = ctypes.c_void_p
         L.bp_create.argtypes = [ctypes.POINTER(vp), c_i, ctypes.c_int32, ctypes.c_int32, c_f,
                                 ctypes.c_float, ctypes.c_int, ctypes.c_float, ctypes.c_int]
+        L.bp_create_striped.argtypes = [ctypes.POINTER(vp), c_i, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, c_f,
+                                        ctypes.c_float, ctypes.c_int, ctypes.c_float, ctypes.c_int]
         L.bp_destroy.argtypes = [vp]
         L.bp_clear.argtypes = [vp]
         L.bp_process_view.argtypes = [vp, c_f, c_f, c_f, vp, ctypes.c_int32, ctypes.c_int32,

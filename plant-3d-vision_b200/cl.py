@@ -106,7 +106,7 @@ class Backprojection(object):
     """
 
     def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
-                 *, device=None, i_range=None):
+                 *, device=None, i_range=None, stripes=None):
         self.shape = shape
         self.origin = origin
         self.voxel_size = voxel_size
@@ -129,6 +129,18 @@ class Backprojection(object):
         nx = int(self.shape[0])
         self.i_range = (0, nx) if i_range is None else (int(i_range[0]), int(i_range[1]))
         self.local_shape = [self.i_range[1] - self.i_range[0], int(self.shape[1]), int(self.shape[2])]
+        # stripes = (lg_block, world, rank): hold the axis-0 planes whose block index (i >> lg_block) is
+        # congruent to rank modulo world (load-balanced multi-GPU sharding, see parallel.py)
+        self.stripes = None
+        if stripes is not None:
+            if i_range is not None:
+                raise ValueError("give i_range or stripes, not both")
+            lg, world, rank = (int(t) for t in stripes)
+            self.stripes = (lg, world, rank)
+            self.planes = np.array([i for i in range(nx) if (i >> lg) % world == rank], dtype=np.int64)
+            self.local_shape[0] = len(self.planes)
+        else:
+            self.planes = np.arange(self.i_range[0], self.i_range[1], dtype=np.int64)
 
         buff_size = int(np.prod(self.local_shape, dtype=np.int64)) * 4
         logger.info(f"Buffer shape is {self.shape}")
@@ -146,9 +158,14 @@ class Backprojection(object):
         shape = (ctypes.c_int32 * 3)(*[int(s) for s in self.shape])
         origin = (ctypes.c_float * 3)(*[float(np.float32(o)) for o in self.origin])
         h = ctypes.c_void_p()
-        _cabi.check(_cabi.lib().bp_create(ctypes.byref(h), shape, self.i_range[0], self.i_range[1], origin,
-                                          float(np.float32(self.voxel_size)), self._mode,
-                                          float(self.default_value), self.device))
+        if self.stripes is not None:
+            _cabi.check(_cabi.lib().bp_create_striped(ctypes.byref(h), shape, *self.stripes, origin,
+                                                      float(np.float32(self.voxel_size)), self._mode,
+                                                      float(self.default_value), self.device))
+        else:
+            _cabi.check(_cabi.lib().bp_create(ctypes.byref(h), shape, self.i_range[0], self.i_range[1], origin,
+                                              float(np.float32(self.voxel_size)), self._mode,
+                                              float(self.default_value), self.device))
         self._h = h
         self._fin = weakref.finalize(self, _cabi.lib().bp_destroy, h)
         return

@@ -147,6 +147,8 @@ def vol2pcd(volume, origin, voxel_size, level_set_value=0, *, device=None, retur
 def _vol2pcd_from_backprojection(bp, origin, voxel_size, level_set_value, return_distance=False):
     """Fused handoff: binarise the handle's raw device state exactly as the reference binarises
     what ``Voxels`` would have written (tasks/cl.py:172-184 then proc3d.py:515)."""
+    if getattr(bp, "stripes", None) is not None:
+        raise ValueError("vol2pcd needs contiguous planes: gather a striped volume first")
     ptr, _, pitch = bp.device_state()
     bp.sync()
     shape = bp.local_shape

@@ -89,7 +89,7 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
     try:
         from plant3dvision_b200.parallel import DistributedBackprojection
         shape, origin, vs, views = scene()
-        if backend == "nccl" and sharding == "slabs":
+        if backend == "nccl" and sharding in ("slabs", "stripes"):
             engine_kwargs["ingest"] = "sharded"  # exercise the NVLink exchange for both kernels at world size 2
         bp = DistributedBackprojection(shape, origin, vs, type=kind, default_value=default_value, log=False,
                                        sharding=sharding, **engine_kwargs)
@@ -105,7 +105,7 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
         assert np.array_equal(bp.get_values(gather=True), vol) or kind == "averaging"
         if kind == "averaging":
             np.testing.assert_allclose(bp.get_values(gather=True), vol, rtol=1e-5, atol=1e-6)
-        if backend == "nccl" and sharding == "slabs":
+        if backend == "nccl" and sharding in ("slabs", "stripes"):
             # masks resident in HBM on every rank (bench.py's `value` leg): sharded pack + all-gather of bit tiles
             bp.clear()
             dev = [torch.from_numpy(v[3]).cuda(rank) for v in views]

@@ -254,6 +254,30 @@ def test_slabs_equal_full_grid(BP, Oracle):
         np.testing.assert_array_equal(np.concatenate(parts, axis=0), want)
 
 
+def test_stripes_equal_full_grid(BP):
+    """Striped handles (blocks of 2^lg planes dealt round robin) hold exactly the planes of a full run."""
+    w, views = synth_views("C2", 0.25, soft=2.0)
+    shape, origin, vs = w["shape"], w["origin"], w["voxel_size"]
+    for kind in ("carving", "averaging"):
+        full = BP(shape, origin, vs, type=kind, log=(kind == "averaging"))
+        full.process_views(views)
+        want = full.get_values().copy()
+        full.close()
+        for lg, world in ((0, 2), (2, 3), (3, 8), (7, 2)):
+            got = np.full_like(want, 77)
+            seen = np.zeros(shape[0], dtype=int)
+            for rank in range(world):
+                s = BP(shape, origin, vs, type=kind, log=(kind == "averaging"), stripes=(lg, world, rank))
+                assert list(s.local_shape) == [len(s.planes), shape[1], shape[2]]
+                s.process_views(views)
+                if len(s.planes):
+                    got[s.planes] = s.get_values()
+                seen[s.planes] += 1
+                s.close()
+            assert (seen == 1).all()
+            np.testing.assert_array_equal(got, want)
+
+
 def test_view_order_independence_of_carving(BP):
     """The final carve state does not depend on view order - the property the
     view-sharded MIN all-reduce relies on."""
@@ -438,7 +462,7 @@ def test_distributed_world_of_one_equals_plain(BP):
 
 
 @pytest.mark.parametrize("kind,sharding", [("carving", "views"), ("carving", "slabs"), ("averaging", "views"),
-                                           ("averaging", "slabs")])
+                                           ("averaging", "slabs"), ("carving", "stripes"), ("averaging", "stripes")])
 def test_two_gpus_nccl_equal_sequential(tmp_path, Oracle, kind, sharding):
     import torch
     if torch.cuda.device_count() < 2:
@@ -456,7 +480,7 @@ def test_two_gpus_nccl_equal_sequential(tmp_path, Oracle, kind, sharding):
         o.process_view(*v)
     for rank in range(2):
         vol = np.load(tmp_path / f"rank{rank}.npz")["vol"]
-        if kind == "carving" or sharding == "slabs":
+        if kind == "carving" or sharding in ("slabs", "stripes"):
             assert np.array_equal(vol, o.get_values())
         else:
             np.testing.assert_allclose(vol, o.get_values(), rtol=1e-5, atol=1e-6)
