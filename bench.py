@@ -409,6 +409,8 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device - the B200 arm has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        from plant3dvision_b200.parallel import bind_to_gpu_numa_node
+        bind_to_gpu_numa_node(local)  # before any pinned allocation: host buffers land on the GPU's own socket
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 

@@ -63,6 +63,32 @@ def decode_carve_state(state, default_value=0):
     return out
 
 
+def bind_to_gpu_numa_node(device):
+    """Pin this process (and therefore its first-touch / pinned host allocations) to the CPUs NVML reports as
+    local to CUDA device ``device``.  With one rank per GPU, host<->device copies then stay on the GPU's own
+    socket and PCIe root complex instead of crossing the inter-socket link.  Returns the CPU list, or None when
+    NVML / affinity information is unavailable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        phys = int(device)
+        if vis and all(x.strip().isdigit() for x in vis.split(",")):
+            phys = int(vis.split(",")[int(device)])
+        h = nv.nvmlDeviceGetHandleByIndex(phys)
+        n_cpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:  # no NVML, no permission, not Linux: leave the scheduler alone
+        return None
+
+
 def _dist():
     import torch.distributed as dist
     return dist

@@ -200,3 +200,24 @@ def test_volume_writers_round_trip(tmp_path):
     volf = np.linspace(0, 1, 4 * 5 * 6, dtype=np.float32).reshape(4, 5, 6)
     tcl.write_volume(p, volf)
     assert np.array_equal(tcl.read_volume(p), volf)
+
+
+def test_pointcloud_task_defaults_and_ply_round_trip(tmp_path):
+    from plant3dvision_b200.tasks import proc3d as tp
+    # plant3dvision/tasks/proc3d.py:60-64
+    assert tp.DEFAULTS == dict(upstream_task="Voxels", level_set_value=1.0, background_prior=1.0,
+                               min_contrast=10.0, min_score=0.2)
+    p = tmp_path / "pipe.toml"
+    p.write_text('[PointCloud]\nupstream_task = "Voxels"\nlevel_set_value = 1\nunknown_key = 3\n')
+    assert tp.load_config(str(p))["level_set_value"] == 1.0
+    with pytest.raises(TypeError):
+        tp.parse_params({"nope": 1})
+    rng = np.random.default_rng(0)
+    pts, nrm, col = rng.random((17, 3)), rng.random((17, 3)), rng.integers(0, 2, (17, 3)).astype(float)
+    tp.write_ply(tmp_path / "a.ply", pts, nrm, col)
+    a, b, c = tp.read_ply(tmp_path / "a.ply")
+    assert np.array_equal(a, pts) and np.array_equal(b, nrm) and np.array_equal(c, (col * 255).astype(np.uint8))
+    tp.write_ply(tmp_path / "b.ply", pts[:0], nrm[:0])
+    a, b, c = tp.read_ply(tmp_path / "b.ply")
+    assert a.shape == (0, 3) and c is None
+    assert open(tmp_path / "a.ply", "rb").read(3) == b"ply"

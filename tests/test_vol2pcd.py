@@ -230,3 +230,47 @@ def test_vol2pcd_c2_size_properties():
     np.testing.assert_allclose(np.linalg.norm(a.normals, axis=1), 1.0, rtol=0, atol=1e-12)
     idx = (a.points - np.asarray(w["origin"])) / w["voxel_size"]
     assert (idx > -3).all() and (idx < np.asarray(w["shape"]) + 3).all()
+
+
+@pytest.mark.gpu
+def test_pointcloud_task_on_a_scan_directory(tmp_path):
+    """Voxels output on disk (TIFF volume / multi-label NPZ + {origin, voxel_size}) -> PointCloud.ply, as
+    tasks/proc3d.py:66-136 does, against the oracle run on the same files."""
+    from oracle import vol2pcd_oracle as vo
+    from plant3dvision_b200 import fsdb_lite
+    from plant3dvision_b200.tasks import proc3d as tp
+    from plant3dvision_b200.tasks.cl import write_volume
+    from test_host_logic import make_scan
+    scan = fsdb_lite.Scan(make_scan(tmp_path))
+    origin, vs = [1.0, 2.0, 3.0], 0.5
+    # single volume, carving values, TIFF
+    vol = np.where(blob((24, 20, 31), seed=1) > 0.5, 1, -1).astype(np.int32)
+    fs = scan.get_fileset("Voxels_0123456789", create=True)
+    f = fs.create_file("Voxels", "tiff")
+    write_volume(f.path(), vol)
+    f.set_metadata({"voxel_size": vs, "origin": origin})
+    out = tp.PointCloud(scan).run()
+    pts, nrm, col = tp.read_ply(out.path())
+    want_p, want_n = vo.vol2pcd(vol, np.array(origin), vs, 1.0)
+    assert col is None and pts.shape == want_p.shape and len(pts) > 100
+    np.testing.assert_allclose(pts, want_p, rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(nrm, want_n, rtol=0, atol=1e-12)
+    assert out.get_metadata("voxel_size") == vs
+    # multiclass NPZ
+    rng = np.random.default_rng(2)
+    vox = {"background": rng.random((24, 20, 31)) * 0.02 + 0.01}
+    for q, l in enumerate(("leaf", "stem")):
+        vox[l] = rng.random((24, 20, 31)) * 0.02 + 0.9 * np.roll(blob((24, 20, 31), seed=3, noise=0.0), 6 * q, axis=2)
+    f2 = scan.get_fileset("Voxels_multi", create=True).create_file("Voxels", "npz")
+    np.savez_compressed(f2.path(), **vox)
+    f2.set_metadata({"voxel_size": vs, "origin": origin})
+    out2 = tp.PointCloud(scan, voxels_file=f2, level_set_value=0.0).run()
+    pts, nrm, col = tp.read_ply(out2.path())
+    sel = vo.multiclass_select(vox)
+    parts = [vo.vol2pcd(sel[l], np.array(origin), vs, 0.0) for l in ("leaf", "stem")]
+    want_p = np.concatenate([p for p, _ in parts])
+    assert pts.shape == want_p.shape and len(pts) > 100 and col is not None
+    np.testing.assert_allclose(pts, want_p, rtol=1e-12, atol=1e-12)
+    labels = out2.get_metadata("labels")
+    assert labels == ["leaf"] * len(parts[0][0]) + ["stem"] * len(parts[1][0])
+    assert (col[:len(parts[0][0])] == [0, 255, 255]).all() and (col[len(parts[0][0]):] == [0, 0, 255]).all()
