@@ -283,7 +283,8 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         # axis-0 slabs; mask ingest sharded over the ranks + one all-gather over NVLink (parallel.py)
         from plant3dvision_b200.parallel import DistributedBackprojection
         bp = DistributedBackprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False,
-                                       sharding="stripes", device=local)
+                                       sharding="stripes", device=local,
+                                       stripe_lg=int(os.environ.get("BP_STRIPE_LG", "3")))
         eng = bp.local
     else:
         bp = eng = Backprojection(w["shape"], w["origin"], w["voxel_size"], type=mode, log=False, device=local,
