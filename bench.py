@@ -212,7 +212,9 @@ def run_reference(args):
     kind = "reference" if bo.have_backend("ref_off") else "port"
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     masks = render_all(w, dev, args.mode, pinned=False)
-    n_pl = args.cpu_planes or auto_planes(w, args.mode)
+    # the reference kernel source (one pass per view over int32 / float32 images it first widens) runs ~20x
+    # slower than the port: size the per-step sample so that `--steps 5 --warmup 3` ends within ~2 minutes
+    n_pl = args.cpu_planes or (max(2, auto_planes(w, args.mode) // 5) if kind == "reference" else auto_planes(w, args.mode))
     planes = sample_planes(w["shape"][0], n_pl)
     for _ in range(min(args.warmup, 1)):
         cpu_leg(w, masks, args.mode, planes[:1], kind)
