@@ -14,8 +14,13 @@ class OracleEngine:
     """Duck-types what ``DistributedBackprojection`` needs from ``cl.Backprojection``."""
 
     def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
-                 i_range=None):
+                 i_range=None, stripes=None):
         from oracle.backprojection_oracle import BackprojectionOracle
+        # stripes = (lg_block, world, rank): the stand-in computes the whole grid and hands out its planes
+        self.planes = None
+        if stripes is not None:
+            lg, world, rank = stripes
+            self.planes = np.array([i for i in range(shape[0]) if (i >> lg) % world == rank])
         self.i_range = i_range or (0, shape[0])
         self.default_value = default_value
         self.type = type
@@ -31,7 +36,8 @@ class OracleEngine:
         self.o.process_view(i, r, t, m)
 
     def get_values(self):
-        return self.o.get_values()
+        vol = self.o.get_values()
+        return vol if self.planes is None else vol[self.planes]
 
     def clear(self):
         self.o.clear()

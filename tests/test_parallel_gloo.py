@@ -29,6 +29,7 @@ def sequential(kind, default_value):
 @pytest.mark.parametrize("kind,sharding,default_value", [
     ("carving", "views", 0), ("carving", "slabs", 0), ("carving", "views", 3),
     ("averaging", "views", 0), ("averaging", "slabs", 0), ("averaging", "views", 0.5),
+    ("carving", "stripes", 0), ("averaging", "stripes", 0),
 ])
 def test_two_ranks_equal_sequential(tmp_path, kind, sharding, default_value):
     import torch.multiprocessing as mp
@@ -37,11 +38,15 @@ def test_two_ranks_equal_sequential(tmp_path, kind, sharding, default_value):
     want = sequential(kind, default_value)
     for rank in range(world):
         z = np.load(tmp_path / f"rank{rank}.npz")
-        if kind == "carving" or sharding == "slabs":
+        if kind == "carving" or sharding in ("slabs", "stripes"):
             assert np.array_equal(z["vol"], want)  # bit-exact
         else:
             np.testing.assert_allclose(z["vol"], want, rtol=1e-5, atol=1e-6)  # summation order changed
         i0, i1 = z["i_range"]
+        if sharding == "stripes":  # blocks of 8 planes dealt round robin (21 planes: rank 0 holds 0-7 and 16-20)
+            planes = [i for i in range(want.shape[0]) if (i >> 3) % world == rank]
+            assert np.array_equal(z["part"], want[planes])
+            continue
         assert (i0, i1) == (parallel.slab_range(want.shape[0], rank, world) if sharding == "slabs" else (0, want.shape[0]))
         if sharding == "slabs":
             assert np.array_equal(z["part"], want[i0:i1])
