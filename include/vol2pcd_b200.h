@@ -82,6 +82,21 @@ int bp_multiclass_select(int device, int n_labels, const void *const *vols, int 
                          double min_contrast, double min_score, int label, void **out_dev);
 int bp_device_free(int device, void *ptr);
 
+/* SURVEY §8f-4 — the scoring loop of the SegmentedPointCloud task (plant3dvision/tasks/proc3d.py:203-228) with
+ * proc3d.backproject_points (plant3dvision/proc3d.py:655-659), which the reference runs as a pure-Python loop
+ * over points inside a loop over files: every point is projected into every label map (float64 pinhole, pixel =
+ * (int)(u + 0.5), no depth test — as the reference), and scores[label][point] += map[y][x] when the pixel is
+ * inside the picture; then labels[point] = argmax over labels (first maximum).
+ *   points   n_points x 3 float64 (host)
+ *   cams     n_views x 16 float64: fx fy cx cy | rotmat row-major | tvec
+ *   maps     n_views host pointers to uint8 H x W label maps, hw n_views x 2 (H, W), view_label n_views
+ *            indices into [0, n_labels)
+ *   scores   out, n_labels x n_points float64 (exact integers), may be NULL; labels out, n_points int32
+ *   ms       out (may be NULL): device time of the scoring kernel                                        */
+int bp_score_points(int device, int64_t n_points, const double *points, int32_t n_views, const double *cams,
+                    const void *const *maps, const int32_t *hw, const int32_t *view_label, int32_t n_labels,
+                    double *scores, int32_t *labels, float *ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -90,3 +90,34 @@ def multiclass_select(voxels, background_prior=1.0, min_contrast=10.0, min_score
             pred_c *= (pred_c > min_score)
             out[l[i]] = pred_c
     return out
+
+
+def backproject_points(points, K, rot, tvec):
+    """proc3d.py:655-659."""
+    x = rot @ points.transpose() + tvec[:, np.newaxis]
+    x = K @ x
+    x = x / x[2, :][np.newaxis, :]
+    return x[:2, :].transpose()
+
+
+def score_points(points, views, labels):
+    """tasks/proc3d.py:203-230 (SegmentedPointCloud.run scoring): ``views`` = [(label, camera dict, mask)], the
+    per-point Python loop vectorised with the same operations.  Returns (pts_labels, scores)."""
+    pts = np.asarray(points)
+    scores = np.zeros((len(labels), len(pts)))
+    for label, camera, mask in views:
+        if label not in labels:
+            continue
+        if camera is None:
+            continue
+        rotmat = np.array(camera["rotmat"])
+        tvec = np.array(camera["tvec"])
+        intrinsics = camera["camera_model"]["params"]
+        K = np.array([[intrinsics[0], 0, intrinsics[2]], [0, intrinsics[1], intrinsics[3]], [0, 0, 1]])
+        with np.errstate(all="ignore"):
+            pixels = np.asarray(backproject_points(pts, K, rotmat, tvec) + 0.5, dtype=int)
+        label_idx = labels.index(label)
+        ok = (pixels[:, 0] >= 0) & (pixels[:, 0] < mask.shape[1]) & (pixels[:, 1] >= 0) & (pixels[:, 1] < mask.shape[0])
+        idx = np.nonzero(ok)[0]
+        scores[label_idx, idx] += mask[pixels[idx, 1], pixels[idx, 0]]
+    return np.argmax(scores, axis=0).flatten(), scores

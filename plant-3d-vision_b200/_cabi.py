@@ -24,7 +24,7 @@ SYMBOLS = [
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
 V2P_SYMBOLS = [
     "bp_vol2pcd", "bp_vol2pcd_info", "bp_vol2pcd_fetch", "bp_vol2pcd_device", "bp_vol2pcd_signed_distance",
-    "bp_vol2pcd_free", "bp_multiclass_select", "bp_device_free",
+    "bp_vol2pcd_free", "bp_multiclass_select", "bp_device_free", "bp_score_points",
 ]
 V2P_U8, V2P_I8, V2P_I32, V2P_F32, V2P_F64 = 0, 1, 2, 3, 4
 V2P_BIN_GT, V2P_BIN_EQ, V2P_BIN_GE = 0, 1, 2
@@ -85,6 +85,8 @@ def lib():
                                            ctypes.c_uint32, c_i, ctypes.c_int, ctypes.c_double, ctypes.c_double,
                                            ctypes.c_double, ctypes.c_int, ctypes.POINTER(vp)]
         L.bp_device_free.argtypes = [ctypes.c_int, vp]
+        L.bp_score_points.argtypes = [ctypes.c_int, ctypes.c_int64, c_d, ctypes.c_int32, c_d, ctypes.POINTER(vp), c_i, c_i,
+                                      ctypes.c_int32, c_d, c_i, c_f]
         for name in V2P_SYMBOLS:
             getattr(L, name).restype = ctypes.c_int
         L.bp_last_error.restype = ctypes.c_char_p

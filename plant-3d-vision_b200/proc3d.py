@@ -225,3 +225,63 @@ def pointcloud_from_voxels(voxels, origin, voxel_size, level_set_value=1.0, back
         nrm.append(out.normals)
         point_labels += [label] * len(out.points)
     return PointCloud(np.concatenate(pts), np.concatenate(nrm)), point_labels
+
+
+# ---------------------------------------------------------------------------------------------------
+# SegmentedPointCloud scoring (plant3dvision/tasks/proc3d.py:185-253)
+# ---------------------------------------------------------------------------------------------------
+def backproject_points(points, K, rot, tvec):
+    """proc3d.py:655-659, verbatim (host numpy; the GPU path below does the same arithmetic per point)."""
+    x = rot @ points.transpose() + tvec[:, np.newaxis]
+    x = K @ x
+    x = x / x[2, :][np.newaxis, :]
+    return x[:2, :].transpose()
+
+
+def score_points(points, views, labels, *, device=None, return_scores=True):
+    """The scoring loops of ``SegmentedPointCloud.run`` (tasks/proc3d.py:203-230) on the GPU.
+
+    ``points``: ``[N, 3]`` float64.  ``views``: sequence of ``(label, camera, mask)`` in file order, ``camera`` the
+    metadata dict the task reads (``rotmat``, ``tvec``, ``camera_model.params``), ``mask`` a 2-D uint8 label map;
+    views whose label is not in ``labels`` or whose camera is ``None`` are skipped like the reference does
+    (tasks/proc3d.py:205-217).  ``labels``: the label list IN THE ORDER the caller wants ties broken (the reference
+    builds it from a Python ``set``, so its order is arbitrary; tasks/proc3d.py:193-201).
+    Returns ``(pts_labels [N] int, scores [L, N] float64 or None, device_ms)``."""
+    L = _cabi.lib()
+    if device is None:
+        import os
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    pts = np.ascontiguousarray(points, dtype=np.float64).reshape(-1, 3)
+    labels = list(labels)
+    cams, maps, hw, vlab = [], [], [], []
+    for label, camera, mask in views:
+        if label not in labels:
+            continue
+        if camera is None:
+            logger.warning("Could not get camera pose for view, skipping...")
+            continue
+        m = np.asarray(mask)
+        if m.ndim != 2 or m.dtype not in (np.uint8, np.bool_):
+            raise TypeError(f"label maps must be 2-D uint8 arrays, got {m.dtype} {m.shape}")
+        m = np.ascontiguousarray(m.view(np.uint8))
+        intr = camera["camera_model"]["params"]
+        cams.append(np.concatenate([np.asarray(intr[0:4], dtype=np.float64),
+                                    np.asarray(camera["rotmat"], dtype=np.float64).reshape(9),
+                                    np.asarray(camera["tvec"], dtype=np.float64).reshape(3)]))
+        maps.append(m)
+        hw.append(m.shape)
+        vlab.append(labels.index(label))
+    n, nv, nl = len(pts), len(maps), max(len(labels), 1)
+    cams_a = np.ascontiguousarray(np.array(cams, dtype=np.float64).reshape(nv, 16))
+    hw_a = np.ascontiguousarray(np.array(hw, dtype=np.int32).reshape(nv, 2))
+    vlab_a = np.ascontiguousarray(np.array(vlab, dtype=np.int32))
+    ptrs = (ctypes.c_void_p * max(nv, 1))(*[m.ctypes.data for m in maps])
+    scores = np.zeros((nl, n), dtype=np.float64) if return_scores else None
+    out = np.zeros(n, dtype=np.int32)
+    ms = ctypes.c_float()
+    D, I = ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int32)
+    _cabi.check(L.bp_score_points(int(device), n, pts.ctypes.data_as(D), nv, cams_a.ctypes.data_as(D), ptrs,
+                                  hw_a.ctypes.data_as(I), vlab_a.ctypes.data_as(I), nl,
+                                  scores.ctypes.data_as(D) if scores is not None else None, out.ctypes.data_as(I),
+                                  ctypes.byref(ms)))
+    return out.astype(np.int64), scores, ms.value

@@ -190,3 +190,87 @@ def run_pointcloud(scan_dir, config=None, **overrides):
         params = parse_params(config, strict=False)
     params.update(overrides)
     return PointCloud(scan_dir, **params).run()
+
+
+class SegmentedPointCloud:
+    """Back-projects 2-D segmentation maps onto an existing point cloud (tasks/proc3d.py:139-253): every point is
+    projected into every label map, the map values are summed per label and the point takes the arg-max label.
+    The reference runs this as a Python loop over points inside a loop over files; here it is one kernel launch
+    (``proc3d.score_points``).
+
+    ``scan``: ``fsdb_lite.Scan`` or path; ``pcd_file`` / ``segmentation_fileset`` default to the first file of the
+    ``PointCloud*`` fileset and to the ``Segmentation2D*`` fileset, as the reference's upstream tasks resolve.
+    The reference builds its label list from a ``set`` (arbitrary order, which decides ties); here the labels are
+    sorted, or given explicitly through ``labels``."""
+
+    def __init__(self, scan, pcd_file=None, segmentation_fileset=None, use_colmap_poses=True, labels=None,
+                 colors=None, upstream_task="PointCloud", upstream_segmentation="Segmentation2D"):
+        self.scan = scan if hasattr(scan, "get_fileset") else fsdb_lite.Scan(scan)
+        self.use_colmap_poses = bool(use_colmap_poses)  # tasks/proc3d.py:160
+        self.upstream_task = upstream_task
+        self.upstream_segmentation = upstream_segmentation
+        self._pcd_file = pcd_file
+        self._seg_fs = segmentation_fileset
+        self._labels = None if labels is None else list(labels)
+        self.colors = dict(DEFAULT_COLORS if colors is None else colors)
+
+    @property
+    def task_id(self):
+        sig = json.dumps({"use_colmap_poses": self.use_colmap_poses, "upstream_task": self.upstream_task,
+                          "upstream_segmentation": self.upstream_segmentation}, sort_keys=True)
+        return "SegmentedPointCloud_" + hashlib.md5(sig.encode()).hexdigest()[:10]
+
+    def _inputs(self):
+        fs = self._seg_fs if self._seg_fs is not None else _find_fileset(self.scan, self.upstream_segmentation)
+        if fs is None:
+            raise IOError(f"No output of '{self.upstream_segmentation}' in scan '{self.scan.id}'")
+        pf = self._pcd_file
+        if pf is None:
+            pfs = _find_fileset(self.scan, self.upstream_task)
+            if pfs is None or not pfs.get_files():
+                raise IOError(f"No output of upstream task '{self.upstream_task}' in scan '{self.scan.id}'")
+            pf = pfs.get_files()[0]
+        return fs, pf
+
+    def label_list(self, fs):
+        """tasks/proc3d.py:192-201."""
+        labels = set()
+        for fi in fs.get_files():
+            label = fi.get_metadata("channel")
+            if label is not None:
+                labels.add(label)
+        labels = sorted(labels) if self._labels is None else list(self._labels)
+        if self._labels is None:
+            labels.remove("background")  # raises like the reference when there is no background channel
+            if "rgb" in labels:
+                labels.remove("rgb")
+        return labels
+
+    def compute(self, device=None):
+        """-> (points, normals, pts_labels [N], labels list, scores [L, N])."""
+        fs, pf = self._inputs()
+        path = pf.path() if callable(getattr(pf, "path", None)) else pf
+        pts, normals, _ = read_ply(path)
+        labels = self.label_list(fs)
+        key = "colmap_camera" if self.use_colmap_poses else "camera"  # tasks/proc3d.py:208-211
+        views = [(fi.get_metadata("channel"), fi.get_metadata(key), fi) for fi in fs.get_files()]
+        views = [(l, c, f.read_image() if (l in labels and c is not None) else None) for l, c, f in views]
+        pts_labels, scores, _ = proc3d.score_points(pts, views, labels, device=device)
+        return pts, normals, pts_labels, labels, scores
+
+    def run(self, device=None):
+        """Writes ``SegmentedPointCloud.ply`` with per-label colours and the ``labels`` metadata
+        (tasks/proc3d.py:231-253)."""
+        pts, normals, pts_labels, labels, _ = self.compute(device=device)
+        rng = np.random.default_rng(0)  # the reference draws np.random.rand(3) for labels without a colour
+        palette = np.array([self.colors[l] if l in self.colors else rng.random(3) for l in labels],
+                           dtype=np.float64).reshape(-1, 3)
+        color_array = palette[pts_labels] if len(labels) else np.zeros((len(pts), 3))
+        point_labels = [labels[i] for i in pts_labels.tolist()]
+        out_fs = self.scan.get_fileset(self.task_id, create=True)
+        f = out_fs.create_file("SegmentedPointCloud", "ply")
+        write_ply(f.path(), pts, normals, color_array)
+        f.set_metadata("labels", point_labels)
+        out_fs.set_metadata({"task_name": "SegmentedPointCloud",
+                             "task_params": {"use_colmap_poses": self.use_colmap_poses}})
+        return f
