@@ -12,11 +12,12 @@ LIB_PATH = os.path.join(_PKG, "libbp_b200.so")
 MODE_CARVING, MODE_AVERAGING = 0, 1
 MASK_U8, MASK_I32, MASK_F32, MASK_U16 = 0, 1, 2, 3
 FLAG_INVERT, FLAG_BOOL_INVERT, FLAG_DEVICE_MASKS, FLAG_PACKED_MASKS = 1, 2, 4, 8
+TAIL_F64, TAIL_EXP_CLIP = 1, 2
 
 # every symbol include/bp_b200.h declares; tests check the library exports all of them
 SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
-    "bp_get_values", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
+    "bp_get_values", "bp_get_values_tail", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
     "bp_pack_views", "bp_packed_size", "bp_create_striped",
 ]
@@ -63,6 +64,8 @@ def lib():
         L.bp_packed_size.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_int64)]
         L.bp_get_values.argtypes = [vp, vp]
         L.bp_get_values_device.argtypes = [vp, vp]
+        L.bp_get_values_tail.argtypes = [vp, vp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_double),
+                                         ctypes.POINTER(ctypes.c_double)]
         L.bp_device_state.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_int64), c_i]
         L.bp_sync.argtypes = [vp]
         L.bp_stream.argtypes = [vp, ctypes.POINTER(vp)]

@@ -399,7 +399,25 @@ class Backprojection(object):
 
     get_volume = get_values  # the name BASELINE.json's north_star uses
 
-    def process_fileset(self, fs, camera_metadata, invert=False):
+    def get_values_tail(self, out=None, float64=False, exp_clip=False):
+        """``get_values`` with the tail of ``Voxels.run`` fused into the read-back (tasks/cl.py:166-174):
+        returns ``(values, vmin, vmax)`` - ``vmin`` / ``vmax`` of the raw values replace the ``np.unique`` sanity
+        check (tasks/cl.py:168); ``float64`` writes the dtype ``process_fileset`` stacks labels into (cl.py:249);
+        ``exp_clip`` applies ``np.exp`` and the clip to 1 of tasks/cl.py:172-174 (averaging only).  ``out`` may be
+        any C-contiguous array of the right size and dtype (e.g. a row of the stacked result); default: a new array
+        (float64) or the pinned ``values_h``."""
+        dt = np.dtype(np.float64) if float64 else self.dtype
+        if out is None:
+            out = np.empty(tuple(self.local_shape), dtype=dt) if float64 else self.values_h
+        if out.dtype != dt or not out.flags["C_CONTIGUOUS"] or out.size != int(np.prod(self.local_shape)):
+            raise ValueError(f"out must be a C-contiguous {dt} array of {int(np.prod(self.local_shape))} elements")
+        lo, hi = ctypes.c_double(), ctypes.c_double()
+        flags = (_cabi.TAIL_F64 if float64 else 0) | (_cabi.TAIL_EXP_CLIP if exp_clip else 0)
+        _cabi.check(_cabi.lib().bp_get_values_tail(self._handle(), out.ctypes.data_as(ctypes.c_void_p), flags,
+                                                   ctypes.byref(lo), ctypes.byref(hi)))
+        return out.reshape(self.local_shape), lo.value, hi.value
+
+    def process_fileset(self, fs, camera_metadata, invert=False, exp_clip=False, stats=None):
         """Processes a whole fileset (cl.py:234-257).
 
         Parameters
@@ -410,19 +428,31 @@ class Backprojection(object):
             Name of the metadata to use to get the camera intrinsics (fx, fy, cx, cy) & poses.
         invert : bool, optional
             If ``True``, invert the values of the mask file to process.
+        exp_clip : bool, optional
+            Not in the reference: fuse the ``np.exp`` + clip of ``Voxels.run`` (tasks/cl.py:172-174) into the
+            read-back.  ``stats``, a dict, receives ``min`` / ``max`` of the raw volume (tasks/cl.py:168).
         """
+        lo_all, hi_all = np.inf, -np.inf
         if self.labels is not None:
             result = np.zeros((len(self.labels), *self.local_shape))
             for i, label in enumerate(self.labels):
                 logger.info(f"Processing label '{label}'...")
                 if i != 0:
                     self.clear()
-                result[i, :] = self.process_label(fs, camera_metadata, label, invert)
-            return result
+                self.process_label(fs, camera_metadata, label, invert, fetch=False)
+                # float64 conversion (exact), min / max and the optional exp + clip happen on the device
+                _, lo, hi = self.get_values_tail(out=result[i], float64=True, exp_clip=exp_clip)
+                lo_all, hi_all = min(lo_all, lo), max(hi_all, hi)  # NaN propagates like numpy's min / max
+                if lo != lo:
+                    lo_all = hi_all = np.nan
         else:
-            return self.process_label(fs, camera_metadata, None, invert=invert)
+            self.process_label(fs, camera_metadata, None, invert=invert, fetch=False)
+            result, lo_all, hi_all = self.get_values_tail(exp_clip=exp_clip)
+        if stats is not None:
+            stats["min"], stats["max"] = lo_all, hi_all
+        return result
 
-    def process_label(self, fs, camera_metadata, label=None, invert=False):
+    def process_label(self, fs, camera_metadata, label=None, invert=False, fetch=True):
         """Processes a whole fileset for given label (cl.py:259-305).
 
         Returns
@@ -452,7 +482,7 @@ class Backprojection(object):
                 self._process_batch(batch, invert)
                 batch = []
         self._process_batch(batch, invert)
-        return self.get_values()
+        return self.get_values() if fetch else None
 
     def clear(self):
         """Re-seed the device grid with ``default_value`` (cl.py:307-311)."""

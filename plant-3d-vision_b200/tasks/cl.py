@@ -22,6 +22,7 @@ import sys
 import numpy as np
 
 from .. import fsdb_lite
+from ..npz_parallel import savez_compressed_parallel
 
 logger = logging.getLogger(__name__)
 
@@ -167,18 +168,17 @@ class Voxels:
 
         sc = Backprojection(shape=shape, origin=origin, voxel_size=float(self.voxel_size), type=str(self.type),
                             labels=labels, log=bool(self.log), **bp_kwargs)
-        vol = sc.process_fileset(masks_files, str(self.camera_metadata), bool(self.invert))
+        # The task tail (tasks/cl.py:166-174) is fused into the read-back: min / max of the raw volume replace the
+        # np.unique sort of :168, np.exp and the clip to 1 of :172-174 run on the device.
+        stats = {}
+        vol = sc.process_fileset(masks_files, str(self.camera_metadata), bool(self.invert),
+                                 exp_clip=bool(self.log and self.type == "averaging"), stats=stats)
         if labels is None:
             vol = vol.copy()  # detach from the pinned buffer before the device handle goes away
         sc.close()
         logger.debug(f"Voxel volume shape: {vol.shape}")
-        if vol.size and vol.min() == vol.max():  # tasks/cl.py:168 (np.unique) without the sort
+        if vol.size and stats["min"] == stats["max"]:
             logger.warning("There is something WRONG with the volume!")
-
-        # If conversion to log was requested, convert back applying `np.exp` (tasks/cl.py:172-174)
-        if self.log and self.type == "averaging":
-            vol = np.exp(vol)
-            vol[vol > 1] = 1.0
         return vol, labels, origin
 
     def run(self, **bp_kwargs):
@@ -188,7 +188,7 @@ class Voxels:
         out_fs = self.scan.get_fileset(self.task_id, create=True)
         if labels is not None:
             f = out_fs.create_file("Voxels", "npz")
-            np.savez_compressed(f.path(), **{label: vol[i, :] for i, label in enumerate(labels)})
+            savez_compressed_parallel(f.path(), {label: vol[i, :] for i, label in enumerate(labels)})
         else:
             f = out_fs.create_file("Voxels", "tiff")
             write_volume(f.path(), vol)

@@ -221,3 +221,32 @@ def test_pointcloud_task_defaults_and_ply_round_trip(tmp_path):
     a, b, c = tp.read_ply(tmp_path / "b.ply")
     assert a.shape == (0, 3) and c is None
     assert open(tmp_path / "a.ply", "rb").read(3) == b"ply"
+
+
+# ---------------------------------------------------------------------------------------------
+# the NPZ writer of the Voxels task tail
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("force_zip64", [False, True])
+def test_parallel_npz_writer_is_read_back_by_numpy(tmp_path, force_zip64):
+    import importlib
+    import zipfile
+    m = importlib.import_module("plant-3d-vision_b200.npz_parallel")
+    rng = np.random.default_rng(0)
+    arrs = {"background": np.clip(np.exp(rng.normal(-3, 2, (40, 50, 60))), 0, 1),
+            "flower": rng.random((50, 60, 7)).astype(np.float32), "empty": np.zeros((0, 3)), "scalar": np.array(3.5),
+            "strided": np.arange(10, dtype=np.int32).reshape(2, 5)[:, ::2], "carve": rng.integers(-1, 2, (30, 30, 30)),
+            "é": np.ones(3, dtype=bool)}
+    p = m.savez_compressed_parallel(tmp_path / "Voxels", arrs, chunk=1 << 14, force_zip64=force_zip64)
+    assert p.endswith("Voxels.npz")
+    with zipfile.ZipFile(p) as z:
+        assert z.testzip() is None
+        assert all(i.compress_type == zipfile.ZIP_DEFLATED for i in z.infolist())
+        assert [i.filename for i in z.infolist()] == [k + ".npy" for k in arrs]
+    with np.load(p) as z:
+        assert z.files == list(arrs)
+        for k, a in arrs.items():
+            assert z[k].dtype == a.dtype and z[k].shape == a.shape and np.array_equal(z[k], a)
+    # same members and contents as numpy's own writer
+    np.savez_compressed(tmp_path / "ref.npz", **arrs)
+    with np.load(tmp_path / "ref.npz") as r, np.load(p) as z:
+        assert r.files == z.files and all(r[k].tobytes() == z[k].tobytes() for k in r.files)
