@@ -28,6 +28,9 @@ V2P_SYMBOLS = [
     "bp_vol2pcd_free", "bp_multiclass_select", "bp_device_free", "bp_score_points",
 ]
 V2P_U8, V2P_I8, V2P_I32, V2P_F32, V2P_F64 = 0, 1, 2, 3, 4
+# every symbol include/masks_b200.h declares (mask producer)
+MASKS_SYMBOLS = ["bp_masks_filter"]
+MASKS_LINEAR, MASKS_EXCESS_GREEN = 0, 1
 V2P_BIN_GT, V2P_BIN_EQ, V2P_BIN_GE = 0, 1, 2
 V2P_FLAG_DEVICE_VOLUME = 1
 
@@ -90,7 +93,10 @@ def lib():
         L.bp_device_free.argtypes = [ctypes.c_int, vp]
         L.bp_score_points.argtypes = [ctypes.c_int, ctypes.c_int64, c_d, ctypes.c_int32, c_d, ctypes.POINTER(vp), c_i, c_i,
                                       ctypes.c_int32, c_d, c_i, c_f]
-        for name in V2P_SYMBOLS:
+        L.bp_masks_filter.argtypes = [ctypes.c_int, ctypes.c_int32, ctypes.POINTER(vp), ctypes.c_int32, ctypes.c_int32,
+                                      ctypes.c_int32, ctypes.c_int, c_d, ctypes.c_double, ctypes.c_int32,
+                                      ctypes.POINTER(ctypes.c_uint8), c_i, ctypes.POINTER(vp), ctypes.POINTER(vp), c_f]
+        for name in V2P_SYMBOLS + MASKS_SYMBOLS:
             getattr(L, name).restype = ctypes.c_int
         L.bp_last_error.restype = ctypes.c_char_p
         L.bp_version.restype = ctypes.c_char_p

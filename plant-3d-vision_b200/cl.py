@@ -23,7 +23,9 @@ There is no CPU fallback: without the built library or a CUDA device, constructi
 """
 import ctypes
 import logging
+import os
 import weakref
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -38,6 +40,8 @@ _I = ctypes.POINTER(ctypes.c_int32)
 
 #: views handed to one bp_process_views call by process_label (host memory bound)
 MAX_VIEWS_PER_CALL = 256
+#: threads decoding mask images ahead of the device in process_label
+DECODE_THREADS = min(16, os.cpu_count() or 1)
 
 
 def img_as_float32(mask):
@@ -463,7 +467,7 @@ class Backprojection(object):
         if hasattr(fs, "get_files"):
             fs = fs.get_files()
 
-        batch = []
+        todo = []
         for fi in fs:
             # Skip file if not of the right label (when defined)
             if label is not None and fi.get_metadata("channel") != label:
@@ -476,12 +480,18 @@ class Backprojection(object):
             intrinsics = np.array(cam["camera_model"]['params'][0:4], dtype=np.float32)
             rot = np.array(sum(cam['rotmat'], []), dtype=np.float32)
             tvec = np.array(cam['tvec'], dtype=np.float32)
-            mask = _read_image(fi)
-            batch.append((intrinsics, rot, tvec, mask))
-            if len(batch) == MAX_VIEWS_PER_CALL:
-                self._process_batch(batch, invert)
-                batch = []
-        self._process_batch(batch, invert)
+            todo.append((intrinsics, rot, tvec, fi))
+        # Mask ingest: the image decode of cl.py:297 runs on a thread pool (PIL / imageio release the
+        # GIL while decoding), one launch-sized batch ahead of the device, in file order.
+        with ThreadPoolExecutor(max_workers=min(DECODE_THREADS, max(len(todo), 1))) as pool:
+            chunks = [todo[o:o + MAX_VIEWS_PER_CALL] for o in range(0, len(todo), MAX_VIEWS_PER_CALL)]
+            pending = [pool.submit(_read_image, t[3]) for t in chunks[0]] if chunks else []
+            for c, chunk in enumerate(chunks):
+                masks = [p.result() for p in pending]
+                pending = [pool.submit(_read_image, t[3]) for t in chunks[c + 1]] if c + 1 < len(chunks) else []
+                self._process_batch([(t[0], t[1], t[2], m) for t, m in zip(chunk, masks)], invert)
+        if not chunks:
+            self._process_batch([], invert)
         return self.get_values() if fetch else None
 
     def clear(self):

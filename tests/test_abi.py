@@ -15,6 +15,7 @@ HEADER = os.path.join(ROOT, "include", "bp_b200.h")
 
 
 V2P_HEADER = os.path.join(ROOT, "include", "vol2pcd_b200.h")
+MASKS_HEADER = os.path.join(ROOT, "include", "masks_b200.h")
 
 
 def declared_functions(header=HEADER):
@@ -43,9 +44,20 @@ def test_vol2pcd_header_matches_binding_and_cites_the_reference():
     assert lib.bp_vol2pcd(None, 0, None, 0, 0, None, 0, 0, 0.5, None, 1.0, 0.0, 0.0, 0.0, None, 4) == -1
 
 
+def test_masks_header_matches_binding_and_cites_the_reference():
+    assert declared_functions(MASKS_HEADER) == sorted(_cabi.MASKS_SYMBOLS)
+    text = open(MASKS_HEADER).read()
+    for cite in ("proc2d.py:69-115", "proc2d.py:118-169", "proc2d.py:172-220", "tasks/proc2d.py:232"):
+        assert cite in text, cite
+    lib = _cabi.lib()
+    assert lib.bp_masks_filter(0, 0, None, 0, 0, 3, 0, None, 0.3, 0, None, None, None, None, None) == -1  # no coefs
+    assert lib.bp_masks_filter(0, 1, None, 4, 4, 2, 1, None, 0.3, 0, None, None, None, None, None) == -1  # 2 channels
+    assert b"channels" in lib.bp_last_error()
+
+
 def test_library_exports_every_declared_symbol():
     lib = _cabi.lib()
-    for name in declared_functions() + declared_functions(V2P_HEADER):
+    for name in declared_functions() + declared_functions(V2P_HEADER) + declared_functions(MASKS_HEADER):
         assert hasattr(lib, name), f"libbp_b200.so does not export {name}"
     # and nothing C++-mangled leaks an unintended bp_* entry point
     assert lib.bp_version().decode().startswith("bp_b200 ")
