@@ -3,7 +3,7 @@
 GPU pipeline (device-timed, volume already in HBM as the carving state) next to the reference's own
 scipy pipeline (oracle/vol2pcd_oracle.py = proc3d.py:490-570) on the host cores.  Prints one JSON line.
 
-    python tools/bench_vol2pcd.py [--scale 1.0] [--level-set 1.0] [--no-cpu]
+    python tests/bench/bench_vol2pcd.py [--scale 1.0] [--level-set 1.0] [--no-cpu]
 """
 import argparse
 import json
