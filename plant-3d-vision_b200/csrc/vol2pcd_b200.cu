@@ -82,20 +82,35 @@ __global__ void binarise_kernel(const T *__restrict__ vol, int16_t *__restrict__
 // of the other class, |in[q]| otherwise — the lower envelope of Felzenszwalb's separable EDT,
 // evaluated by direct search because the window is tiny.
 // ---------------------------------------------------------------------------------------------
+//
+// Most voxels of a real volume are far from any class boundary and keep the value "far" through all three
+// passes.  They are recognised per 8^3 brick: `near` holds, for every brick, the OR of the class bits (1 =
+// foreground present, 2 = background present) over all bricks within ceil(R / 8) bricks along every axis, i.e. over
+// a neighbourhood that contains every voxel within Chebyshev distance R.  A voxel whose entry is not 3 has only
+// its own class within reach: every value its window could read is "far", in every pass, so its result is its
+// input and the window search (2 R loads) is skipped - exactly, not approximately.
 __global__ void edt_pass_kernel(const int16_t *__restrict__ in, int16_t *__restrict__ out, size_t n,
-                                int axis, int nx, int ny, int nz, int R) {
+                                int axis, int nx, int ny, int nz, int R, const uint32_t *__restrict__ near,
+                                int nbj, int nbk) {
     const size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= n) return;
+    const size_t t = o / (size_t)nz;
+    const int k = (int)(o - t * (size_t)nz);
+    const int i = (int)(t / (size_t)ny), j = (int)(t - (size_t)i * ny);
+    const int s = in[o];
+    if (near[((size_t)(i / kBrick) * nbj + (j / kBrick)) * nbk + (k / kBrick)] != 3u) {
+        out[o] = (int16_t)s;
+        return;
+    }
     int a, len;
     long long stride;
     if (axis == 2) {
-        a = (int)(o % (size_t)nz); len = nz; stride = 1;
+        a = k; len = nz; stride = 1;
     } else if (axis == 1) {
-        a = (int)((o / (size_t)nz) % (size_t)ny); len = ny; stride = nz;
+        a = j; len = ny; stride = nz;
     } else {
-        a = (int)(o / ((size_t)nz * ny)); len = nx; stride = (long long)nz * ny;
+        a = i; len = nx; stride = (long long)nz * ny;
     }
-    const int s = in[o];
     const bool fg = s > 0;
     int best = s > 0 ? s : -s;
     for (int d = 1; d <= R; ++d) {
@@ -114,6 +129,42 @@ __global__ void edt_pass_kernel(const int16_t *__restrict__ in, int16_t *__restr
     }
     best = min(best, kFar);
     out[o] = (int16_t)(fg ? best : -best);
+}
+
+// class bits per 8^3 brick from the binarised volume: one warp per 32-voxel word of a row (= 4 bricks along k)
+__global__ void brick_summary_kernel(const int16_t *__restrict__ s, uint32_t *__restrict__ summary, size_t n_words,
+                                     int ny, int nz, int nw, int nbj, int nbk) {
+    const size_t w = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= n_words) return;
+    const size_t row = w / (size_t)nw;
+    const int kw = (int)(w - row * (size_t)nw);
+    const int k = kw * 32 + lane;
+    const bool valid = k < nz;
+    const bool fg = valid && s[row * (size_t)nz + k] > 0;
+    const uint32_t fb = __ballot_sync(0xffffffffu, fg), vb = __ballot_sync(0xffffffffu, valid);
+    if (lane < 4) {
+        const uint32_t f = (fb >> (8 * lane)) & 0xffu, g = ((vb & ~fb) >> (8 * lane)) & 0xffu;
+        const uint32_t v = (f ? 1u : 0u) | (g ? 2u : 0u);
+        if (v) {
+            const int i = (int)(row / (size_t)ny), j = (int)(row - (size_t)i * ny);
+            uint32_t *p = summary + ((size_t)(i / kBrick) * nbj + (j / kBrick)) * nbk + (kw * 4 + lane);
+            if ((*p & v) != v) atomicOr(p, v);
+        }
+    }
+}
+
+// out[b] = OR of in over the bricks within r along one axis (three passes = the box neighbourhood)
+__global__ void brick_or_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, int nbi, int nbj, int nbk,
+                                int axis, int r) {
+    const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= (size_t)nbi * nbj * nbk) return;
+    const int k = (int)(b % (size_t)nbk), j = (int)((b / (size_t)nbk) % (size_t)nbj), i = (int)(b / ((size_t)nbk * nbj));
+    const int a = axis == 2 ? k : axis == 1 ? j : i, len = axis == 2 ? nbk : axis == 1 ? nbj : nbi;
+    const long long stride = axis == 2 ? 1 : axis == 1 ? nbk : (long long)nbk * nbj;
+    uint32_t v = 0;
+    for (int d = max(-r, -a); d <= min(r, len - 1 - a) && v != 3u; ++d) v |= in[(long long)b + d * stride];
+    out[b] = v;
 }
 
 // signed, half-voxel-shifted distance (proc3d.py:522): dist - 0.5 inside, -mdist + 0.5 outside
@@ -475,21 +526,35 @@ int bp_vol2pcd(v2p_result **out, int device, const void *vol, int vol_dtype, uin
     if (rc) return rc;
     const unsigned nb = (unsigned)((n + 255) / 256);
     CUV(cudaEventRecord(sc.ev[1]));
-    edt_pass_kernel<<<nb, 256>>>(s0, s1, n, 2, nx, ny, nz, R);
-    edt_pass_kernel<<<nb, 256>>>(s1, s0, n, 1, nx, ny, nz, R);
-    edt_pass_kernel<<<nb, 256>>>(s0, s1, n, 0, nx, ny, nz, R);
-    CUV(cudaGetLastError());
-    CUV(cudaEventRecord(sc.ev[2]));
-    r->launches += 4;
-    int16_t *s = s1;
-
-    // band words, output slots, active bricks
+    // brick class summary and its box dilation by ceil(R / 8) bricks (see edt_pass_kernel)
     const int nw = (nz + 31) / 32;
     const size_t n_words = (size_t)nx * ny * nw;
     const int nbi = (nx + kBrick - 1) / kBrick, nbj = (ny + kBrick - 1) / kBrick, nbk = (nw * 32) / kBrick;
     const size_t n_bricks = (size_t)nbi * nbj * nbk;
     if (n_words >= 0x7fffffffull || n_bricks >= 0x7fffffffull)
         return bp_fail(BP_EINVAL, "volume too large for one call (%zu words)", n_words);
+    uint32_t *near0 = nullptr, *near1 = nullptr;
+    if (sc.alloc(&near0, n_bricks * 4) != cudaSuccess || sc.alloc(&near1, n_bricks * 4) != cudaSuccess)
+        return bp_fail(BP_ENOMEM, "cudaMalloc for the brick summary failed");
+    CUV(cudaMemsetAsync(near0, 0, n_bricks * 4));
+    brick_summary_kernel<<<(unsigned)((n_words * 32 + 255) / 256), 256>>>(s0, near0, n_words, ny, nz, nw, nbj, nbk);
+    {
+        const int rb = (R + kBrick - 1) / kBrick;
+        const unsigned gb = (unsigned)((n_bricks + 255) / 256);
+        brick_or_kernel<<<gb, 256>>>(near0, near1, nbi, nbj, nbk, 2, rb);
+        brick_or_kernel<<<gb, 256>>>(near1, near0, nbi, nbj, nbk, 1, rb);
+        brick_or_kernel<<<gb, 256>>>(near0, near1, nbi, nbj, nbk, 0, rb);
+    }
+    const uint32_t *near = near1;
+    edt_pass_kernel<<<nb, 256>>>(s0, s1, n, 2, nx, ny, nz, R, near, nbj, nbk);
+    edt_pass_kernel<<<nb, 256>>>(s1, s0, n, 1, nx, ny, nz, R, near, nbj, nbk);
+    edt_pass_kernel<<<nb, 256>>>(s0, s1, n, 0, nx, ny, nz, R, near, nbj, nbk);
+    CUV(cudaGetLastError());
+    CUV(cudaEventRecord(sc.ev[2]));
+    r->launches += 8;
+    int16_t *s = s1;
+
+    // band words, output slots, active bricks
     uint32_t *bits = nullptr, *counts = nullptr, *offs = nullptr, *bricks = nullptr;
     uint8_t *brick_flag = nullptr;
     int *n_sel = nullptr;
