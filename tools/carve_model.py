@@ -150,6 +150,62 @@ def main():
     out["dense_views_after_the_first"] = float((t_dense - np.minimum(t_dense, 1)).mean())
     full = (pat[:, 0] >= nv)
     out["warps_fully_inside_the_hull"] = float(full.mean())
+
+    # (a') the conservative patch-versus-view test planned for round 2, evaluated for real on the first views: project
+    # the 4 corners of the patch (it is planar: one plane i), take the pixel bounding box with a 1-pixel margin, and
+    # look the covered 32 x 32 tiles up in a coarse "tile has a set bit" bitmap (here via a summed-area table).
+    # Checks that the test never culls a patch with a surviving voxel, and how many patches it retires.
+    def corners(v):
+        c = cams[v]
+        R, t = c[4:13].reshape(3, 3), c[13:16]
+        ii = np.arange(nx, dtype=np.float32)[:, None, None]
+        jj = (np.arange(nyp // 4, dtype=np.float32) * 4)[None, :, None]
+        kk = (np.arange(nzp // 32, dtype=np.float32) * 32)[None, None, :]
+        us, vs_, zs = [], [], []
+        for dj in (0, 3):
+            for dk in (0, 31):
+                x = ox + ii * vs
+                y = oy + np.minimum(jj + dj, ny - 1) * vs
+                z = oz + np.minimum(kk + dk, nz - 1) * vs
+                px = R[0, 0] * x + R[0, 1] * y + R[0, 2] * z + t[0]
+                py = R[1, 0] * x + R[1, 1] * y + R[1, 2] * z + t[1]
+                pz = R[2, 0] * x + R[2, 1] * y + R[2, 2] * z + t[2]
+                with np.errstate(all="ignore"):
+                    us.append(px / pz * c[0] + c[2])
+                    vs_.append(py / pz * c[1] + c[3])
+                zs.append(pz)
+        return np.stack(us), np.stack(vs_), np.stack(zs)
+
+    Wt, Ht = (w["W"] + 31) // 32, (w["H"] + 31) // 32
+    alive_pat = np.ones(n_w, dtype=bool)
+    first = d.reshape(nx, nyp // 4, 4, nzp // 32, 32).transpose(0, 1, 3, 2, 4).reshape(-1, 128)
+    culled_total, wrong = 0, 0
+    for pos in range(4):
+        v = order[pos]
+        m = masks[v] != 0
+        coarse = np.zeros((Ht * 32, Wt * 32), dtype=bool)
+        coarse[:w["H"], :w["W"]] = m
+        coarse = coarse.reshape(Ht, 32, Wt, 32).any(axis=(1, 3))
+        sat = np.zeros((Ht + 1, Wt + 1), dtype=np.int64)
+        sat[1:, 1:] = coarse.cumsum(0).cumsum(1)
+        u, vv, zz = corners(v)
+        ok = np.isfinite(u).all(0) & np.isfinite(vv).all(0) & (zz.min(0) > 1e-3)
+        u0, u1 = np.floor(u.min(0) - 1), np.floor(u.max(0) + 1)
+        v0, v1 = np.floor(vv.min(0) - 1), np.floor(vv.max(0) + 1)
+        ok &= (u0 >= 0) & (v0 >= 0) & (u1 <= w["W"] - 1) & (v1 <= w["H"] - 1)
+        tx0, tx1 = np.clip(u0 // 32, 0, Wt - 1).astype(np.int64), np.clip(u1 // 32, 0, Wt - 1).astype(np.int64)
+        ty0, ty1 = np.clip(v0 // 32, 0, Ht - 1).astype(np.int64), np.clip(v1 // 32, 0, Ht - 1).astype(np.int64)
+        cnt = sat[ty1 + 1, tx1 + 1] - sat[ty0, tx1 + 1] - sat[ty1 + 1, tx0] + sat[ty0, tx0]
+        cull = (ok & (cnt == 0)).reshape(-1) & alive_pat
+        # every real voxel of a culled patch must have died at or before this view
+        bad = cull & ((first > pos).any(axis=1))
+        wrong += int(bad.sum())
+        dies_here = alive_pat & (first.max(axis=1) <= pos)
+        out[f"cull_view{pos}_culled"] = float(cull.sum() / n_w)
+        out[f"cull_view{pos}_patches_dead_after_it"] = float(dies_here.sum() / n_w)
+        culled_total += int(cull.sum())
+        alive_pat &= ~dies_here
+    out["cull_wrong_decisions"] = wrong
     print(json.dumps(out))
 
 
