@@ -1,0 +1,66 @@
+"""The argument the carve kernel rests on, checked on its own (CPU): the reference's per-view state machine
+(kernels/backprojection.c:57-84, run view after view by cl.py:190-227) has an ORDER-INDEPENDENT result that equals a
+MINIMUM over per-view outcomes in the device coding 0 carved < 1 seen < 2 unseen.  That is what lets the kernel
+(i) visit the views in farthest-point order, (ii) test several views of one voxel at the same time in the sparse
+phase and combine them with `min`, (iii) MIN-all-reduce view-sharded replicas, and (iv) expand to the reference's
+int32 values only at read-back (`expand_state_kernel` / `tail_kernel`), for every seed value of the grid.
+"""
+import numpy as np
+import pytest
+
+MISS, ZERO, NONZERO = 2, 0, 1  # outcome of one voxel against one view, already in the device coding
+
+
+def reference_sequential(outcomes, default_value):
+    """kernels/backprojection.c:57-84 applied view after view to one voxel."""
+    s = default_value
+    for o in outcomes:
+        if s == -1:       # :65-67 carved voxels return at once
+            continue
+        if o == MISS:     # :70-72 outside the picture / behind the camera: state untouched
+            continue
+        if o == ZERO:     # :79-80
+            s = -1
+        elif s == 0:      # :81-83 `seen` only promotes a grid value of 0
+            s = 1
+    return s
+
+
+def device_result(outcomes, default_value, rng):
+    """min-combine over an arbitrary order and an arbitrary grouping into simultaneous passes, then the read-back
+    expansion of csrc/bp_b200.cu (values_to_device)."""
+    order = rng.permutation(len(outcomes))
+    st, q = 2, 0
+    while q < len(order):
+        g = int(rng.choice([1, 2, 4, 8, 16, 32]))
+        if st == 0:
+            break                                    # a carved voxel is skipped for the remaining views
+        st = min([st] + [outcomes[v] for v in order[q:q + g]])
+        q += g
+    d = default_value
+    if d == -1:
+        return -1
+    return {0: -1, 1: 1 if d == 0 else d, 2: d}[st]
+
+
+@pytest.mark.parametrize("default_value", [0, 1, 5, -1, -3])
+def test_min_combine_in_any_order_equals_the_sequential_state_machine(default_value):
+    rng = np.random.default_rng(default_value + 10)
+    for trial in range(3000):
+        n = int(rng.integers(0, 12))
+        p = rng.dirichlet([1, 1, 1])
+        outcomes = [int(o) for o in rng.choice([MISS, ZERO, NONZERO], size=n, p=p)]
+        assert device_result(outcomes, default_value, rng) == reference_sequential(outcomes, default_value), outcomes
+
+
+def test_replicas_min_reduce_like_the_sequential_run():
+    """View sharding: every rank carves its own views from the seed; the element-wise MIN of the int8
+    states is the single-GPU state.  (Plain min over the reference's -1 / 0 / 1 would be wrong: min(0, 1) = 0.)"""
+    rng = np.random.default_rng(0)
+    for trial in range(2000):
+        n, world = int(rng.integers(1, 10)), int(rng.integers(1, 5))
+        outcomes = [int(o) for o in rng.choice([MISS, ZERO, NONZERO], size=n)]
+        ranks = [min([2] + outcomes[r::world]) for r in range(world)]
+        st = min(ranks)
+        assert {0: -1, 1: 1, 2: 0}[st] == reference_sequential(outcomes, 0)
+    assert min(0, 1) == 0 and reference_sequential([NONZERO], 0) == 1  # the counter-example for the naive coding
