@@ -66,6 +66,17 @@ def ncu_traffic(mode):
     return None
 
 
+def ncu_counters(mode):
+    """The other ncu counters of the same committed capture (L2 bytes and GB/s, issue-slot utilisation, hit
+    rates), or None.  Static evidence from profiles/, not measured by this run."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return (json.load(f).get("ncu") or {}).get(mode)
+    except (OSError, ValueError):
+        return None
+
+
 class ClockSampler:
     """SM clock and throttle reasons DURING the timed region, sampled every ~5 ms through NVML in a
     thread (same counters as the nvidia-smi clocks line of B200_PROFILING.md; nvidia-smi itself cannot
@@ -343,7 +354,7 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
     roofline = {
         "bound": "hbm", "kernel": "carve_kernel" if mode == "carving" else "average_kernel<u8>",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": ncu_traffic(mode), "peak_source": peak_src,
+        "traffic": ncu_traffic(mode), "ncu": ncu_counters(mode), "peak_source": peak_src,
         "kernel_ms_per_launch": k_ms / n_launch_per_step, "ingest_ms_per_step": float(tmax[2]) / args.steps,
         "algorithmic_bytes_per_launch": algo_bytes,
         "note": "algorithmic bytes = SURVEY 8(d) per-view streaming traffic (4 B/voxel-view carving, 8 B averaging, "
