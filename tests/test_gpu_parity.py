@@ -128,6 +128,26 @@ def test_synthetic_carving(BP, Oracle, name, scale):
     assert (want == 1).sum() > 0 and (want == -1).sum() > 0
 
 
+@pytest.mark.parametrize("p_zero", [0.01, 0.08, 0.5])
+def test_speckle_masks_walk_every_warp_through_every_live_count(BP, Oracle, p_zero):
+    """Random salt-and-pepper masks: every view carves a random p_zero of the voxels it sees, so the number of live
+    voxels of each warp patch decays 128 -> 0 through every value and in random lane patterns.  This drives the
+    dense -> medium (two survivors per lane) -> sparse (g views at a time, re-dealing) hand-offs of carve_kernel
+    through all their cases (structured phantoms leave most patches either full or empty)."""
+    from plant3dvision_b200 import synth
+    w = synth.workload("C2", 0.2)
+    rng = np.random.default_rng(int(p_zero * 1000))
+    views = [(*split_cam(w["cams"][v]), np.where(rng.random((w["H"], w["W"])) < p_zero, 0, 255).astype(np.uint8))
+             for v in range(len(w["cams"]))]
+    got, want = run_both(BP, Oracle, w["shape"], w["origin"], w["voxel_size"], views, "carving")
+    assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ"
+    live = (want != -1).mean()
+    assert (want == -1).any() and (p_zero > 0.05 or live > 0.3)  # slow decay keeps patches above 32 live for long
+    # the streaming path (one launch per view: every hand-off restarts from the stored state) agrees too
+    got1, want1 = run_both(BP, Oracle, w["shape"], w["origin"], w["voxel_size"], views[:12], "carving", fused=False)
+    assert np.array_equal(got1, want1)
+
+
 @pytest.mark.parametrize("log", [False, True])
 def test_synthetic_averaging(BP, Oracle, log):
     w, views = synth_views("C2", 0.25, soft=2.0)
