@@ -313,8 +313,10 @@ class DistributedBackprojection(object):
         self._reduced = False
         return self.get_values(gather=gather)
 
-    def process_fileset(self, fs, camera_metadata, invert=False, gather=True):
-        """cl.py:234-257 distributed (float64 ``[L, ...]`` stack when labels are set)."""
+    def process_fileset(self, fs, camera_metadata, invert=False, gather=True, exp_clip=False, stats=None):
+        """cl.py:234-257 distributed (float64 ``[L, ...]`` stack when labels are set).  ``exp_clip`` / ``stats``: the
+        same contract as ``Backprojection.process_fileset`` (the tail of ``Voxels.run``, tasks/cl.py:166-174); here
+        the min / max are combined over the ranks and ``np.exp`` + clip run on the host after the exchange."""
         if self.labels is not None:
             result = None
             for i, label in enumerate(self.labels):
@@ -324,8 +326,28 @@ class DistributedBackprojection(object):
                 if result is None:
                     result = np.zeros((len(self.labels), *vol.shape))
                 result[i, :] = vol
-            return result
-        return self.process_label(fs, camera_metadata, None, invert=invert, gather=gather)
+        else:
+            result = self.process_label(fs, camera_metadata, None, invert=invert, gather=gather)
+        if stats is not None:
+            lo = float(result.min()) if result.size else np.inf
+            hi = float(result.max()) if result.size else -np.inf
+            if self.world > 1 and not (gather or self.sharding == "views"):
+                import torch
+                dist = _dist()
+                nccl = str(dist.get_backend(self.group)) == "nccl"
+                dev = torch.device("cuda", int(getattr(self.local, "device", 0))) if nccl else torch.device("cpu")
+                t = torch.tensor([-lo, hi], dtype=torch.float64, device=dev)  # NaN propagates through MAX
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                lo, hi = -float(t[0]), float(t[1])
+            stats["min"], stats["max"] = lo, hi
+        if exp_clip:
+            if self.type != "averaging":
+                raise ValueError("exp/clip applies to averaging volumes only (tasks/cl.py:172)")
+            if self.labels is None:
+                result = result.copy()  # get_values aliases a reused host buffer
+            np.exp(result, out=result)
+            result[result > 1] = 1.0
+        return result
 
     # -- combination ---------------------------------------------------------------------------
     def reduce(self):

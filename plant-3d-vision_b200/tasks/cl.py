@@ -138,9 +138,14 @@ class Voxels:
                 bbox = images.get_metadata("bounding_box")
         return bbox
 
-    def compute(self, **bp_kwargs):
-        """Everything of ``run`` up to (not including) writing: returns (vol, labels, origin)."""
-        from ..cl import Backprojection
+    def compute(self, backprojection_class=None, **bp_kwargs):
+        """Everything of ``run`` up to (not including) writing: returns (vol, labels, origin).
+        ``backprojection_class``: the engine, ``plant3dvision_b200.cl.Backprojection`` by default;
+        ``plant3dvision_b200.parallel.DistributedBackprojection`` under ``torchrun`` shards the grid or the views
+        over the ranks (its keyword arguments - ``sharding=...`` - go through ``bp_kwargs``)."""
+        if backprojection_class is None:
+            from ..cl import Backprojection as backprojection_class
+        Backprojection = backprojection_class
         masks_fileset = self._masks_fileset or _find_fileset(self.scan, self.upstream_mask)
         if masks_fileset is None:
             raise IOError(f"No fileset found for upstream task '{self.upstream_mask}' in scan '{self.scan.id}'")
@@ -175,16 +180,20 @@ class Voxels:
                                  exp_clip=bool(self.log and self.type == "averaging"), stats=stats)
         if labels is None:
             vol = vol.copy()  # detach from the pinned buffer before the device handle goes away
+        self._rank = int(getattr(sc, "rank", 0))
         sc.close()
         logger.debug(f"Voxel volume shape: {vol.shape}")
         if vol.size and stats["min"] == stats["max"]:
             logger.warning("There is something WRONG with the volume!")
         return vol, labels, origin
 
-    def run(self, **bp_kwargs):
+    def run(self, backprojection_class=None, **bp_kwargs):
         """Run and write the output fileset: ``Voxels.npz`` (one array per label) or ``Voxels.tiff``
-        / ``Voxels.npy`` plus the file metadata ``{voxel_size, origin}`` (tasks/cl.py:176-186)."""
-        vol, labels, origin = self.compute(**bp_kwargs)
+        / ``Voxels.npy`` plus the file metadata ``{voxel_size, origin}`` (tasks/cl.py:176-186).  With a distributed
+        engine every rank computes and rank 0 writes (the others return ``None``)."""
+        vol, labels, origin = self.compute(backprojection_class, **bp_kwargs)
+        if getattr(self, "_rank", 0) != 0:
+            return None
         out_fs = self.scan.get_fileset(self.task_id, create=True)
         if labels is not None:
             f = out_fs.create_file("Voxels", "npz")
@@ -223,12 +232,13 @@ def read_volume(path):
         return np.stack([np.asarray(p) for p in ImageSequence.Iterator(im)])
 
 
-def run_voxels(scan_dir, config=None, **overrides):
+def run_voxels(scan_dir, config=None, backprojection_class=None, bp_kwargs=None, **overrides):
     """``romi_run_task Voxels <scan_dir> --config <toml>`` without luigi: ``config`` is a TOML path
-    or an already parsed ``[Voxels]`` dict."""
+    or an already parsed ``[Voxels]`` dict.  ``backprojection_class`` / ``bp_kwargs``: see ``Voxels.compute``
+    (e.g. ``DistributedBackprojection`` with ``{"sharding": "stripes"}`` under ``torchrun``)."""
     if isinstance(config, (str, os.PathLike)):
         params = load_config(config)
     else:
         params = parse_params(config, strict=False)
     params.update(overrides)
-    return Voxels(scan_dir, **params).run()
+    return Voxels(scan_dir, **params).run(backprojection_class, **(bp_kwargs or {}))

@@ -134,3 +134,29 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
             assert np.array_equal(bp.get_values(gather=True), a)
     finally:
         dist.destroy_process_group()
+
+
+def worker_voxels_task(rank, world, port, scan_dir, sharding, out_dir):
+    """The Voxels task mirror over a distributed engine: every rank computes, rank 0 writes."""
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from plant3dvision_b200.parallel import DistributedBackprojection
+        from plant3dvision_b200.tasks import cl as tcl
+        out = tcl.run_voxels(scan_dir, {"type": "averaging", "voxel_size": 1.0, "log": True, "camera_metadata": "camera",
+                                        "upstream_mask": "ImagesFilesetExists", "labels": ["stem", "background"]},
+                             backprojection_class=DistributedBackprojection,
+                             bp_kwargs={"engine": OracleEngine, "sharding": sharding})
+        assert (out is None) == (rank != 0)
+        # the distributed tail contract on its own: local planes, min / max agreed over the ranks
+        from plant3dvision_b200 import fsdb_lite
+        files = fsdb_lite.Scan(scan_dir).get_fileset("images").get_files()
+        bp = DistributedBackprojection([9, 7, 5], [-4.0, -3.0, -2.0], 1.0, type="averaging", labels=["stem"], log=True,
+                                       sharding="slabs", engine=OracleEngine)
+        st = {}
+        part = bp.process_fileset(files, "camera", gather=False, exp_clip=True, stats=st)
+        np.savez(os.path.join(out_dir, f"tail{rank}.npz"), part=part, lo=st["min"], hi=st["max"], i_range=np.array(bp.i_range))
+    finally:
+        dist.destroy_process_group()

@@ -86,3 +86,40 @@ def test_bad_arguments():
         parallel.DistributedBackprojection([2, 2, 2], [0, 0, 0], 1.0, sharding="nope")
     with pytest.raises(ValueError):
         parallel.DistributedBackprojection([2, 2, 2], [0, 0, 0], 1.0, type="nope")
+
+
+@pytest.mark.parametrize("sharding", ["views", "stripes"])
+def test_voxels_task_over_a_distributed_engine(tmp_path, sharding):
+    """`run_voxels(..., backprojection_class=DistributedBackprojection)` on two ranks: rank 0 writes the same
+    Voxels.npz a single process writes (tasks/cl.py:149-186), the tail (exp + clip, min / max) included."""
+    import torch.multiprocessing as mp
+    from _gloo_worker import worker_voxels_task
+    from test_host_logic import make_scan
+    from test_tasks_cpu import OracleEngine as SingleEngine
+    from plant3dvision_b200 import fsdb_lite
+    scan_dir = str(make_scan(tmp_path, n=4, channels=("background", "stem")))
+    world = 2
+    mp.spawn(worker_voxels_task, args=(world, free_port(), scan_dir, sharding, str(tmp_path)), nprocs=world, join=True)
+    scan = fsdb_lite.Scan(scan_dir)
+    outs = [fs for fs in scan.get_filesets() if fs.id.startswith("Voxels_")]
+    assert len(outs) == 1 and [f.filename for f in outs[0].get_files()] == ["Voxels.npz"]
+    files = scan.get_fileset("images").get_files()
+    eng = SingleEngine([9, 7, 5], [-4.0, -3.0, -2.0], 1.0, type="averaging", labels=["stem", "background"], log=True)
+    st = {}
+    want = eng.process_fileset(files, "camera", exp_clip=True, stats=st)
+    with np.load(outs[0].get_files()[0].path()) as z:
+        assert z.files == ["stem", "background"]
+        for i, l in enumerate(z.files):
+            if sharding == "views":  # float32 sums in another order, then exp
+                np.testing.assert_allclose(z[l], want[i], rtol=1e-5, atol=1e-7)
+            else:
+                assert np.array_equal(z[l], want[i])
+    # local planes + agreed min / max
+    raw = SingleEngine([9, 7, 5], [-4.0, -3.0, -2.0], 1.0, type="averaging", labels=["stem"], log=True)
+    st1 = {}
+    full = raw.process_fileset(files, "camera", exp_clip=True, stats=st1)
+    for rank in range(world):
+        z = np.load(tmp_path / f"tail{rank}.npz")
+        i0, i1 = z["i_range"]
+        assert np.array_equal(z["part"], full[:, i0:i1])
+        assert float(z["lo"]) == st1["min"] and float(z["hi"]) == st1["max"]
