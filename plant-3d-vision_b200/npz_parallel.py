@@ -111,7 +111,8 @@ def savez_compressed_parallel(file, arrays, level=6, threads=None, chunk=CHUNK, 
                 f.write(ex)
             cd_size = f.tell() - cd_off
             n_ent = len(central)
-            big = force_zip64 or n_ent >= 0xFFFF or cd_off >= _MAX32 or cd_size >= _MAX32
+            # (an empty archive stays a bare end-of-central-directory record: numpy recognises it by its magic)
+            big = (force_zip64 and n_ent > 0) or n_ent >= 0xFFFF or cd_off >= _MAX32 or cd_size >= _MAX32
             if big:
                 z_off = f.tell()
                 f.write(struct.pack("<IQHHIIQQQQ", 0x06064B50, 44, 45, 45, 0, 0, n_ent, n_ent, cd_size, cd_off))

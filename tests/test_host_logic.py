@@ -250,3 +250,28 @@ def test_parallel_npz_writer_is_read_back_by_numpy(tmp_path, force_zip64):
     np.savez_compressed(tmp_path / "ref.npz", **arrs)
     with np.load(tmp_path / "ref.npz") as r, np.load(p) as z:
         assert r.files == z.files and all(r[k].tobytes() == z[k].tobytes() for k in r.files)
+
+
+def test_parallel_npz_writer_property(tmp_path):
+    """Random dtypes / shapes / chunk sizes (chunk boundaries inside and across members, empty and 0-d arrays)."""
+    import importlib
+    from hypothesis import given, settings, strategies as st
+    from hypothesis.extra import numpy as hnp
+    m = importlib.import_module("plant-3d-vision_b200.npz_parallel")
+    dtypes = st.sampled_from([np.float64, np.float32, np.int32, np.int8, np.uint8, np.bool_, np.int64, np.complex64])
+    arrays = st.dictionaries(st.text("abcdefgh_", min_size=1, max_size=6),
+                             dtypes.flatmap(lambda d: hnp.arrays(d, hnp.array_shapes(min_dims=0, max_dims=3, min_side=0, max_side=9))),
+                             min_size=0, max_size=4)
+    counter = [0]
+
+    @settings(max_examples=40, deadline=None)
+    @given(arrays, st.sampled_from([1, 7, 64, 4096]), st.booleans(), st.integers(1, 3))
+    def check(arrs, chunk, z64, threads):
+        counter[0] += 1
+        p = m.savez_compressed_parallel(tmp_path / f"a{counter[0]}", arrs, chunk=chunk, force_zip64=z64, threads=threads)
+        with np.load(p) as z:
+            assert sorted(z.files) == sorted(arrs)
+            for k, a in arrs.items():
+                assert z[k].dtype == a.dtype and z[k].shape == a.shape and z[k].tobytes() == a.tobytes()
+
+    check()
