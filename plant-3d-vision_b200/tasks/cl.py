@@ -206,6 +206,10 @@ class Voxels:
         return f
 
 
+#: volumes at least this large are written as BigTIFF by the PIL fallback of ``write_volume``
+BIGTIFF_BYTES = 2 ** 32 - 2 ** 24
+
+
 def write_volume(path, vol):
     """Multi-page TIFF, one page per axis-0 plane - the layout imageio gives plantdb's
     ``io.write_volume`` (io.py:491-525).  Uses tifffile / imageio when present, else PIL."""
@@ -217,7 +221,10 @@ def write_volume(path, vol):
         pass
     from PIL import Image
     pages = [Image.fromarray(np.ascontiguousarray(vol[i])) for i in range(vol.shape[0])]
-    pages[0].save(path, format="TIFF", save_all=True, append_images=pages[1:])
+    # classic TIFF holds 32-bit offsets: a 1024^3 int32 volume (4.29 GB) needs BigTIFF, which is what
+    # tifffile / imageio switch to on their own
+    big = vol.nbytes + 4096 * len(pages) >= BIGTIFF_BYTES
+    pages[0].save(path, format="TIFF", save_all=True, append_images=pages[1:], **({"big_tiff": True} if big else {}))
 
 
 def read_volume(path):

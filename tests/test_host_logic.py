@@ -275,3 +275,21 @@ def test_parallel_npz_writer_property(tmp_path):
                 assert z[k].dtype == a.dtype and z[k].shape == a.shape and z[k].tobytes() == a.tobytes()
 
     check()
+
+
+def test_volume_writer_switches_to_bigtiff_for_large_volumes(tmp_path, monkeypatch):
+    """A 1024^3 int32 volume does not fit the 32-bit offsets of classic TIFF; the threshold is lowered here so that
+    the BigTIFF branch runs on a small array."""
+    import struct
+    vol = np.random.default_rng(1).integers(-1, 2, (6, 5, 7)).astype(np.int32)
+    tcl.write_volume(tmp_path / "classic.tiff", vol)
+    monkeypatch.setattr(tcl, "BIGTIFF_BYTES", 100)
+    tcl.write_volume(tmp_path / "big.tiff", vol)
+    version = lambda p: struct.unpack("<H", open(p, "rb").read(4)[2:4])[0]
+    try:
+        import tifffile  # noqa: F401  (tifffile chooses by itself; nothing to check)
+    except ImportError:
+        assert version(tmp_path / "classic.tiff") == 42 and version(tmp_path / "big.tiff") == 43
+    for name in ("classic.tiff", "big.tiff"):
+        back = tcl.read_volume(tmp_path / name)
+        assert back.dtype == vol.dtype and np.array_equal(back, vol)
