@@ -265,10 +265,11 @@ def test_parallel_npz_writer_property(tmp_path):
     counter = [0]
 
     @settings(max_examples=40, deadline=None)
-    @given(arrays, st.sampled_from([1, 7, 64, 4096]), st.booleans(), st.integers(1, 3))
-    def check(arrs, chunk, z64, threads):
+    @given(arrays, st.sampled_from([1, 7, 64, 4096]), st.booleans(), st.integers(1, 3), st.sampled_from([1, 2, None]))
+    def check(arrs, chunk, z64, threads, window):
         counter[0] += 1
-        p = m.savez_compressed_parallel(tmp_path / f"a{counter[0]}", arrs, chunk=chunk, force_zip64=z64, threads=threads)
+        p = m.savez_compressed_parallel(tmp_path / f"a{counter[0]}", arrs, chunk=chunk, force_zip64=z64, threads=threads,
+                                        window=window)
         with np.load(p) as z:
             assert sorted(z.files) == sorted(arrs)
             for k, a in arrs.items():
