@@ -17,6 +17,8 @@ normals; multiclass clouds also carry uchar red green blue) plus the file metada
 import hashlib
 import json
 import logging
+import os
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -203,6 +205,9 @@ class SegmentedPointCloud:
     The reference builds its label list from a ``set`` (arbitrary order, which decides ties); here the labels are
     sorted, or given explicitly through ``labels``."""
 
+    #: label-map pixels (bytes) decoded and uploaded per device call
+    CHUNK_BYTES = 2 << 30
+
     def __init__(self, scan, pcd_file=None, segmentation_fileset=None, use_colmap_poses=True, labels=None,
                  colors=None, upstream_task="PointCloud", upstream_segmentation="Segmentation2D"):
         self.scan = scan if hasattr(scan, "get_fileset") else fsdb_lite.Scan(scan)
@@ -253,9 +258,31 @@ class SegmentedPointCloud:
         pts, normals, _ = read_ply(path)
         labels = self.label_list(fs)
         key = "colmap_camera" if self.use_colmap_poses else "camera"  # tasks/proc3d.py:208-211
-        views = [(fi.get_metadata("channel"), fi.get_metadata(key), fi) for fi in fs.get_files()]
-        views = [(l, c, f.read_image() if (l in labels and c is not None) else None) for l, c, f in views]
-        pts_labels, scores, _ = proc3d.score_points(pts, views, labels, device=device)
+        todo = []
+        for fi in fs.get_files():
+            label, camera = fi.get_metadata("channel"), fi.get_metadata(key)
+            if label not in labels:
+                continue
+            if camera is None:
+                logger.warning("Could not get camera pose for view, skipping...")
+                continue
+            todo.append((label, camera, fi))
+        # Label maps are decoded on a thread pool and scored in chunks of at most CHUNK_BYTES of pixels, so that host
+        # and device memory stay bounded for large scans; the per-label sums are exact integers, so adding the
+        # chunks' scores and taking the arg-max at the end equals one pass over all files.
+        scores = np.zeros((len(labels), len(pts)))
+        with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as pool:
+            q = 0
+            while labels and q < len(todo):
+                first = np.asarray(todo[q][2].read_image())
+                per = max(first.size, 1)
+                e = min(len(todo), q + max(1, int(self.CHUNK_BYTES // per)))
+                imgs = [first] + list(pool.map(lambda t: np.asarray(t[2].read_image()), todo[q + 1:e]))
+                views = [(t[0], t[1], im) for t, im in zip(todo[q:e], imgs)]
+                _, part, _ = proc3d.score_points(pts, views, labels, device=device)
+                scores += part
+                q = e
+        pts_labels = np.argmax(scores, axis=0).flatten() if len(labels) else np.zeros(len(pts), dtype=np.int64)
         return pts, normals, pts_labels, labels, scores
 
     def run(self, device=None):

@@ -115,9 +115,8 @@ def test_segmented_point_cloud_task_host_logic(tmp_path, monkeypatch):
 
     def fake_score(points, views, labels, *, device=None, return_scores=True):
         seen["labels"] = list(labels)
-        seen["views"] = [(l, c is not None, None if m is None else m.shape) for l, c, m in views]
-        kept = [(l, c, m) for l, c, m in views if l in labels and c is not None]
-        lab, sc = vo.score_points(points, kept, list(labels))
+        seen.setdefault("calls", []).append([(l, c is not None, m.shape) for l, c, m in views])
+        lab, sc = vo.score_points(points, views, list(labels))
         return lab, sc, 0.0
 
     monkeypatch.setattr(proc3d, "score_points", fake_score)
@@ -143,8 +142,15 @@ def test_segmented_point_cloud_task_host_logic(tmp_path, monkeypatch):
     task = tp.SegmentedPointCloud(str(scan_dir), use_colmap_poses=False)
     out = task.run()
     assert seen["labels"] == ["leaf", "stem"]  # background and rgb removed (tasks/proc3d.py:198-201), sorted
-    # images are only decoded for the views that will be scored
-    assert all((shape is not None) == (l in ("leaf", "stem") and has_cam) for l, has_cam, shape in seen["views"])
+    # only the views that will be scored are decoded and handed over: 2 poses x 2 labels, in file order
+    assert seen["calls"] == [[("stem", True, (12, 16)), ("leaf", True, (12, 16))] * 2]
+    # chunked scoring (bounded memory) adds up to the same labels
+    one_shot = out.get_metadata("labels")
+    seen["calls"] = []
+    monkeypatch.setattr(tp.SegmentedPointCloud, "CHUNK_BYTES", 12 * 16 * 3)
+    assert tp.SegmentedPointCloud(str(scan_dir), use_colmap_poses=False).run().get_metadata("labels") == one_shot
+    assert [len(c) for c in seen["calls"]] == [3, 1]
+    monkeypatch.setattr(tp.SegmentedPointCloud, "CHUNK_BYTES", 2 << 30)
     labels = out.get_metadata("labels")
     assert len(labels) == 200 and set(labels) <= {"leaf", "stem"}
     got_pts, _, col = tp.read_ply(out.path())
@@ -152,6 +158,7 @@ def test_segmented_point_cloud_task_host_logic(tmp_path, monkeypatch):
     want = {"leaf": [0, 255, 255], "stem": [0, 0, 255]}
     assert all((col[i] == want[l]).all() for i, l in enumerate(labels))
     # explicit label order decides ties; colmap poses requested but absent -> every view skipped -> all label 0
+    seen["calls"] = []
     out2 = tp.SegmentedPointCloud(str(scan_dir), use_colmap_poses=True, labels=["stem", "leaf"]).run()
-    assert seen["labels"] == ["stem", "leaf"] and set(out2.get_metadata("labels")) == {"stem"}
+    assert seen["calls"] == [] and set(out2.get_metadata("labels")) == {"stem"}  # all-zero scores: first label
     assert out2.id == "SegmentedPointCloud"
