@@ -515,6 +515,26 @@ class Backprojection(object):
         _cabi.check(_cabi.lib().bp_timing(self._handle(), ctypes.byref(k), ctypes.byref(g), ctypes.byref(n)))
         return k.value, g.value, n.value
 
+    def ingest_bytes(self):
+        """Mask bytes copied host -> device on this handle since creation (see bp_ingest_bytes)."""
+        n = ctypes.c_int64()
+        _cabi.check(_cabi.lib().bp_ingest_bytes(self._handle(), ctypes.byref(n)))
+        return n.value
+
+    @staticmethod
+    def view_rect(shape, origin, voxel_size, cam, H, W, planes=None):
+        """``(x0, y0, x1, y1)``: the pixels of a view that the voxels of the grid (or of its axis-0 planes
+        ``planes = (begin, end)``) can project to (see bp_view_rect; host only, needs no GPU).  ``cam`` is the 16-float
+        row ``fx fy cx cy | rot | tvec``."""
+        shp = np.asarray(shape, dtype=np.int32)
+        b, e = (0, int(shp[0])) if planes is None else (int(planes[0]), int(planes[1]))
+        org = np.ascontiguousarray(origin, dtype=np.float32)
+        c = np.ascontiguousarray(cam, dtype=np.float32).reshape(16)
+        rect = np.zeros(4, dtype=np.int32)
+        _cabi.check(_cabi.lib().bp_view_rect(shp.ctypes.data_as(_I), b, e, org.ctypes.data_as(_F), float(voxel_size),
+                                             c.ctypes.data_as(_F), int(H), int(W), rect.ctypes.data_as(_I)))
+        return tuple(int(v) for v in rect)
+
     def device_state(self):
         """(device pointer, bytes, nz pitch) of the raw state (see bp_device_state)."""
         p, nb, pitch = ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_int32()
