@@ -374,10 +374,12 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
         for _ in range(2):
             vol = step_e2e()
         barrier()
+        moved0 = eng.ingest_bytes()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             vol = step_e2e()
         barrier()
+        moved = (eng.ingest_bytes() - moved0) // args.steps  # what the library actually copied up
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
@@ -386,6 +388,10 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
                "h2d_bytes_per_step": int(n_views * H * W) * (world if getattr(bp, "last_ingest", None) == "replicated" else 1),
                "ingest": getattr(bp, "last_ingest", None) or "single GPU",
                "d2h_bytes_per_step": int(nx * ny * nz * 4), "ms_per_step": 1e3 * float(dt[0]) / args.steps}
+        if world == 1 and os.environ.get("BP_VIEW_RECT", "0") not in ("", "0"):
+            # experimental: only the rectangle of each mask that the grid projects into crosses PCIe (bp_view_rect)
+            e2e["h2d_bytes_per_step"] = int(moved)
+            e2e["ingest"] = "single GPU, view rectangles"
     else:
         step_resident()
         vol = bp.get_values(gather=False) if world > 1 else bp.get_values()
