@@ -19,7 +19,7 @@ SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
     "bp_get_values", "bp_get_values_tail", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
-    "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect",
+    "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect", "bp_pack_views_cams",
 ]
 
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
@@ -64,6 +64,8 @@ def lib():
                                        ctypes.c_int, ctypes.c_uint32, c_f]
         L.bp_pack_views.argtypes = [vp, ctypes.c_int32, ctypes.POINTER(vp), c_i, ctypes.c_int, ctypes.c_uint32, vp,
                                     ctypes.c_int64]
+        L.bp_pack_views_cams.argtypes = [vp, ctypes.c_int32, c_f, ctypes.POINTER(vp), c_i, ctypes.c_int, ctypes.c_uint32,
+                                         vp, ctypes.c_int64]
         L.bp_packed_size.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_int64)]
         L.bp_get_values.argtypes = [vp, vp]
         L.bp_get_values_device.argtypes = [vp, vp]

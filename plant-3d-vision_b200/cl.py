@@ -355,9 +355,11 @@ class Backprojection(object):
         _cabi.check(_cabi.lib().bp_packed_size(int(H), int(W), ctypes.byref(n)))
         return n.value
 
-    def pack_views(self, masks, dst_ptr, view_stride, invert=False, device_masks=False, hw=None):
+    def pack_views(self, masks, dst_ptr, view_stride, invert=False, device_masks=False, hw=None, cams=None):
         """Upload + bit-pack ``masks`` (2-D uint8 / bool arrays, or with ``device_masks`` device addresses of
-        uint8 arrays whose sizes are ``hw``) to ``dst_ptr + q * view_stride`` in device memory.  Carving only."""
+        uint8 arrays whose sizes are ``hw``) to ``dst_ptr + q * view_stride`` in device memory.  Carving only.
+        ``cams`` (float32 ``[n, 16]``, optional): lets the library trim each view to the rectangle the whole grid
+        projects into when ``BP_VIEW_RECT=1`` (bp_pack_views_cams)."""
         n = len(masks)
         if n == 0:
             return
@@ -380,6 +382,12 @@ class Backprojection(object):
                 keep.append(arr)
                 hw[q] = arr.shape
                 ptrs[q] = arr.ctypes.data
+        if cams is not None:
+            cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(n, 16)
+            _cabi.check(_cabi.lib().bp_pack_views_cams(self._handle(), n, cams.ctypes.data_as(_F), ptrs,
+                                                       hw.ctypes.data_as(_I), code, flags,
+                                                       ctypes.c_void_p(int(dst_ptr)), int(view_stride)))
+            return
         _cabi.check(_cabi.lib().bp_pack_views(self._handle(), n, ptrs, hw.ctypes.data_as(_I), code, flags,
                                               ctypes.c_void_p(int(dst_ptr)), int(view_stride)))
 

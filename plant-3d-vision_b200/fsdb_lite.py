@@ -20,6 +20,15 @@ def _load_json(path):
     return {}
 
 
+def _dump_json(path, obj):
+    """Write-then-rename, so that a concurrent reader (another rank of a distributed task reading the scan while
+    rank 0 writes its output fileset) sees the old or the new file, never a truncated one."""
+    tmp = f"{path}.tmp{os.getpid()}"
+    with open(tmp, "w") as f:
+        json.dump(obj, f, indent=4)
+    os.replace(tmp, path)
+
+
 def _get(md, key, default):
     if key is None:
         return md
@@ -48,8 +57,7 @@ class File:
         self.metadata.update(data)
         d = os.path.join(self.fileset.scan.dir, "metadata", self.fileset.id)
         os.makedirs(d, exist_ok=True)
-        with open(os.path.join(d, self.id + ".json"), "w") as f:
-            json.dump(self._md, f, indent=4)
+        _dump_json(os.path.join(d, self.id + ".json"), self._md)
 
     def path(self):
         return os.path.join(self.fileset.scan.dir, self.fileset.id, self.filename)
@@ -82,8 +90,7 @@ class Fileset:
             data = {data: value}
         self.metadata.update(data)
         os.makedirs(os.path.join(self.scan.dir, "metadata"), exist_ok=True)
-        with open(os.path.join(self.scan.dir, "metadata", self.id + ".json"), "w") as f:
-            json.dump(self._md, f, indent=4)
+        _dump_json(os.path.join(self.scan.dir, "metadata", self.id + ".json"), self._md)
 
     def get_files(self, query=None):
         """All files whose metadata match every key/value of ``query`` (fsdb.py:2735-2791)."""
@@ -145,5 +152,4 @@ class Scan:
     def _save(self):
         info = {"filesets": [{"id": fs.id, "files": [{"id": f.id, "file": f.filename} for f in fs.files]}
                              for fs in self.filesets]}
-        with open(os.path.join(self.dir, "files.json"), "w") as f:
-            json.dump(info, f, indent=4)
+        _dump_json(os.path.join(self.dir, "files.json"), info)

@@ -22,6 +22,7 @@ class takes it as a parameter only so that the sharding logic can be exercised o
 in the tests with a stand-in engine.
 """
 import logging
+import os
 
 import numpy as np
 
@@ -218,7 +219,11 @@ class DistributedBackprojection(object):
                 cur.wait_event(done[ci & 1])      # NCCL / copies must not overwrite what a pass still reads
             if carving:
                 # (the engine's own stream is already ordered behind that pass)
-                self.local.pack_views([masks[v] for v in mine], buf[r].data_ptr(), stride, invert=invert)
+                # experimental (BP_VIEW_RECT=1): with the cameras the library uploads and packs only the rectangle of
+                # each view that the whole grid projects into
+                rect = os.environ.get("BP_VIEW_RECT", "0") not in ("", "0")
+                self.local.pack_views([masks[v] for v in mine], buf[r].data_ptr(), stride, invert=invert,
+                                      **({"cams": np.asarray(cams, dtype=np.float32).reshape(-1, 16)[mine]} if rect else {}))
                 ev = torch.cuda.Event()
                 ev.record(eng)
                 cur.wait_event(ev)

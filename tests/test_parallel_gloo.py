@@ -18,6 +18,20 @@ def free_port():
         return s.getsockname()[1]
 
 
+def spawn(fn, world, *args):
+    """mp.spawn(fn, (world, port, *args)); a rendezvous that lost its port to another process between free_port()
+    and the bind (or hit a lingering socket) is retried on a fresh port - anything else fails at once."""
+    import torch.multiprocessing as mp
+    for attempt in range(3):
+        try:
+            return mp.spawn(fn, args=(world, free_port(), *args), nprocs=world, join=True)
+        except Exception as e:  # noqa: BLE001 - the child's traceback arrives as text
+            text = str(e).lower()
+            if attempt == 2 or not any(k in text for k in ("address already in use", "eaddrinuse", "connection refused",
+                                                           "connection reset", "timed out", "timeout")):
+                raise
+
+
 def sequential(kind, default_value):
     shape, origin, vs, views = scene()
     o = BackprojectionOracle(shape, origin, vs, type=kind, default_value=default_value)
@@ -32,9 +46,8 @@ def sequential(kind, default_value):
     ("carving", "stripes", 0), ("averaging", "stripes", 0),
 ])
 def test_two_ranks_equal_sequential(tmp_path, kind, sharding, default_value):
-    import torch.multiprocessing as mp
     world = 2
-    mp.spawn(worker, args=(world, free_port(), kind, sharding, default_value, str(tmp_path)), nprocs=world, join=True)
+    spawn(worker, world, kind, sharding, default_value, str(tmp_path))
     want = sequential(kind, default_value)
     for rank in range(world):
         z = np.load(tmp_path / f"rank{rank}.npz")
@@ -92,14 +105,13 @@ def test_bad_arguments():
 def test_voxels_task_over_a_distributed_engine(tmp_path, sharding):
     """`run_voxels(..., backprojection_class=DistributedBackprojection)` on two ranks: rank 0 writes the same
     Voxels.npz a single process writes (tasks/cl.py:149-186), the tail (exp + clip, min / max) included."""
-    import torch.multiprocessing as mp
     from _gloo_worker import worker_voxels_task
     from test_host_logic import make_scan
     from test_tasks_cpu import OracleEngine as SingleEngine
     from plant3dvision_b200 import fsdb_lite
     scan_dir = str(make_scan(tmp_path, n=4, channels=("background", "stem")))
     world = 2
-    mp.spawn(worker_voxels_task, args=(world, free_port(), scan_dir, sharding, str(tmp_path)), nprocs=world, join=True)
+    spawn(worker_voxels_task, world, scan_dir, sharding, str(tmp_path))
     scan = fsdb_lite.Scan(scan_dir)
     outs = [fs for fs in scan.get_filesets() if fs.id.startswith("Voxels_")]
     assert len(outs) == 1 and [f.filename for f in outs[0].get_files()] == ["Voxels.npz"]
