@@ -131,3 +131,26 @@ def test_camera_inside_the_grid_and_mixed_sizes(rect_on):
     for v in views:
         ora.process_view(*v)
     assert np.array_equal(got, ora.get_values())
+
+
+@pytest.mark.parametrize("kind,sharding", [("carving", "slabs"), ("carving", "stripes"), ("averaging", "stripes")])
+def test_two_gpus_sharded_ingest(rect_on, tmp_path, kind, sharding):
+    """The sharded ingest of parallel.py with rectangles: a rank packs its share of the views trimmed to the WHOLE
+    grid's rectangle (bp_pack_views_cams), the tiles are all-gathered, every rank carves its planes from them."""
+    import socket
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    from _gloo_worker import scene, worker
+    from oracle.backprojection_oracle import BackprojectionOracle
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(worker, args=(2, port, kind, sharding, 0, str(tmp_path), "nccl"), nprocs=2, join=True)  # inherits the env
+    shape, origin, vs, views = scene()
+    o = BackprojectionOracle(shape, origin, vs, type=kind)
+    for v in views:
+        o.process_view(*v)
+    for rank in range(2):
+        assert np.array_equal(np.load(tmp_path / f"rank{rank}.npz")["vol"], o.get_values())
