@@ -19,7 +19,7 @@ SYMBOLS = [
     "bp_create", "bp_destroy", "bp_clear", "bp_process_view", "bp_process_views",
     "bp_get_values", "bp_get_values_tail", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
-    "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect", "bp_pack_views_cams",
+    "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect", "bp_pack_views_cams", "bp_set_readback_target", "bp_spec_stats",
 ]
 
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
@@ -77,6 +77,8 @@ def lib():
         L.bp_timing.argtypes = [vp, c_f, c_f, ctypes.POINTER(ctypes.c_int64)]
         L.bp_selftest_division.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64,
                                            ctypes.POINTER(ctypes.c_uint64)]
+        L.bp_set_readback_target.argtypes = [vp, vp]
+        L.bp_spec_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
         L.bp_ingest_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_int64)]
         L.bp_view_rect.argtypes = [c_i, ctypes.c_int32, ctypes.c_int32, c_f, ctypes.c_float, c_f, ctypes.c_int32,
                                    ctypes.c_int32, c_i]

@@ -65,6 +65,12 @@ def img_as_float32(mask):
     raise TypeError(f"Unsupported mask dtype {mask.dtype}")
 
 
+def _destroy_handle(h, keep):
+    """Finaliser of a handle: the device work first, then the pinned buffers it may still be writing to."""
+    _cabi.lib().bp_destroy(h)
+    keep.clear()
+
+
 class _PinnedArray:
     """numpy view over page-locked host memory from ``bp_host_alloc``."""
 
@@ -171,7 +177,9 @@ class Backprojection(object):
                                               float(np.float32(self.voxel_size)), self._mode,
                                               float(self.default_value), self.device))
         self._h = h
-        self._fin = weakref.finalize(self, _cabi.lib().bp_destroy, h)
+        self._keep = []  # pinned buffers registered with the handle (speculative read-back) outlive it
+        self._spec_registered = False
+        self._fin = weakref.finalize(self, _destroy_handle, h, self._keep)
         return
 
     @property
@@ -189,6 +197,7 @@ class Backprojection(object):
             self._fin.detach()
             _cabi.lib().bp_destroy(self._h)
             self._h = None
+            self._keep.clear()
 
     def __enter__(self):
         return self
@@ -286,9 +295,28 @@ class Backprojection(object):
         for s in range(0, len(views), MAX_VIEWS_PER_CALL):
             self._process_batch(views[s:s + MAX_VIEWS_PER_CALL], invert)
 
+    def _register_readback_target(self):
+        """``BP_SPEC_READBACK=1`` (experimental): tell the library where ``get_values`` will want the carve volume, so
+        that it can send an early copy while masks are still being uploaded (bp_set_readback_target)."""
+        if (self._spec_registered or self._mode != _cabi.MODE_CARVING
+                or os.environ.get("BP_SPEC_READBACK", "0") in ("", "0")):
+            return
+        buf = self.values_h
+        if buf.size:
+            _cabi.check(_cabi.lib().bp_set_readback_target(self._handle(), ctypes.c_void_p(buf.ctypes.data)))
+            self._keep.append(self._values)
+        self._spec_registered = True
+
+    def spec_stats(self):
+        """(rows written, rows compared) by the last speculative ``get_values`` (bp_spec_stats)."""
+        a, b = ctypes.c_int64(), ctypes.c_int64()
+        _cabi.check(_cabi.lib().bp_spec_stats(self._handle(), ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
     def _process_batch(self, views, invert):
         if not views:
             return
+        self._register_readback_target()
         n = len(views)
         cams = np.empty((n, 16), dtype=np.float32)
         hw = np.empty((n, 2), dtype=np.int32)
