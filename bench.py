@@ -392,6 +392,10 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
             # experimental: only the rectangle of each mask that the grid projects into crosses PCIe (bp_view_rect)
             e2e["h2d_bytes_per_step"] = int(moved)
             e2e["ingest"] = "single GPU, view rectangles"
+        if world == 1 and mode == "carving" and os.environ.get("BP_SPEC_READBACK", "0") not in ("", "0"):
+            # experimental: early D2H under the uploads, then only the rows that changed (bp_set_readback_target)
+            patched, rows = eng.spec_stats()
+            e2e["readback"] = {"kind": "speculative", "rows_patched": int(patched), "rows": int(rows)}
     else:
         step_resident()
         vol = bp.get_values(gather=False) if world > 1 else bp.get_values()
