@@ -6,7 +6,7 @@
 #      bench with the speculative read-back (BP_SPEC_READBACK=1, tests/test_gpu_spec_readback.py) alone and with both,
 #   4. compute-sanitizer memcheck / racecheck / initcheck of one small carve + average (the fused
 #      kernels stage through shared memory and shuffle survivors between lanes) - smoke() is the workload.
-# Usage: gpurun --timeout 1500 -- 'bash tools/gpu_round2_open.sh'
+# Usage: gpurun --timeout 2400 -- 'bash tools/gpu_round2_open.sh'   (about 20 GPU-minutes)
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
