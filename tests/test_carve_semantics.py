@@ -64,3 +64,26 @@ def test_replicas_min_reduce_like_the_sequential_run():
         st = min(ranks)
         assert {0: -1, 1: 1, 2: 0}[st] == reference_sequential(outcomes, 0)
     assert min(0, 1) == 0 and reference_sequential([NONZERO], 0) == 1  # the counter-example for the naive coding
+
+
+def test_speculative_readback_invariant():
+    """The argument bp_set_readback_target rests on (csrc/bp_b200.cu, start_/finish_spec_readback), on the CPU: the
+    host volume holds the expansion of a SNAPSHOT of the int8 state; later views only ever lower a voxel's state
+    (2 unseen -> 1 seen -> 0 carved); rewriting every (i, j) row whose state differs from the snapshot - padding
+    included in the comparison, excluded from the write - leaves exactly the expansion of the final state."""
+    rng = np.random.default_rng(11)
+    ni, ny, nz, nzp = 5, 7, 37, 48
+    for default_value in (0, 5, -1):
+        d = default_value
+        lut = np.array([-1, -1 if d == -1 else (1 if d == 0 else d), d], dtype=np.int32)  # carve_values()
+        snap = rng.integers(0, 3, (ni * ny, nzp)).astype(np.int8)
+        snap[:, nz:] = rng.integers(-128, 127, (ni * ny, nzp - nz))          # padding holds anything, in both copies
+        final = snap.copy()
+        rows = rng.random(ni * ny) < 0.3                                    # some rows change after the snapshot
+        lower = rng.integers(0, 3, (ni * ny, nz)).astype(np.int8)
+        final[rows, :nz] = np.minimum(final[rows, :nz], lower[rows])
+        host = lut[snap[:, :nz]]                                            # the early copy
+        differs = (final != snap).any(axis=1)                               # patch_rows_kernel's test (whole row)
+        assert not differs[~rows].any()
+        host[differs] = lut[final[differs, :nz]]
+        assert np.array_equal(host, lut[final[:, :nz]])
