@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE — not product code.  Only tests/, __graft_entry__.smoke() and
  * bench.py's cpu_baseline / --impl reference legs may load this library.
  *
- * CPU restatement (plain C, OpenMP over grid planes) of the reference's voxel
+ * CPU restatement (plain C, OpenMP over grid (plane, row) pairs) of the reference's voxel
  * back-projection, one call per view exactly as Backprojection.process_view does
  * (plant3dvision/cl.py:190-227 launches one work-item per voxel per view).
  *
@@ -27,6 +27,9 @@
  */
 #include <stdint.h>
 #include <limits.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 typedef struct {
     float fx, fy, cx, cy;
@@ -77,10 +80,10 @@ void oracle_carve_view(const uint8_t *mask, int H, int W, int32_t *state,
                        int i_offset) {
     const bp_cam c = load_cam(intr, rot, tvec);
     const int nx = shape[0], ny = shape[1], nz = shape[2];
-#pragma omp parallel for schedule(dynamic, 1)
+#pragma omp parallel for collapse(2) schedule(dynamic, 8)
     for (int i = 0; i < nx; ++i) {
-        const float x = origin[0] + (i + i_offset) * voxel_size;
         for (int j = 0; j < ny; ++j) {
+            const float x = origin[0] + (i + i_offset) * voxel_size;
             const float y = origin[1] + j * voxel_size;
             int32_t *row = state + ((int64_t)i * ny + j) * nz;
             for (int k = 0; k < nz; ++k) {
@@ -103,10 +106,10 @@ void oracle_average_view(const float *mask, int H, int W, float *value,
                          int i_offset) {
     const bp_cam c = load_cam(intr, rot, tvec);
     const int nx = shape[0], ny = shape[1], nz = shape[2];
-#pragma omp parallel for schedule(dynamic, 1)
+#pragma omp parallel for collapse(2) schedule(dynamic, 8)
     for (int i = 0; i < nx; ++i) {
-        const float x = origin[0] + (i + i_offset) * voxel_size;
         for (int j = 0; j < ny; ++j) {
+            const float x = origin[0] + (i + i_offset) * voxel_size;
             const float y = origin[1] + j * voxel_size;
             float *row = value + ((int64_t)i * ny + j) * nz;
             for (int k = 0; k < nz; ++k) {
@@ -129,10 +132,10 @@ void oracle_average_view_lut(const uint8_t *mask, const float *lut, int H, int W
                              int i_offset) {
     const bp_cam c = load_cam(intr, rot, tvec);
     const int nx = shape[0], ny = shape[1], nz = shape[2];
-#pragma omp parallel for schedule(dynamic, 1)
+#pragma omp parallel for collapse(2) schedule(dynamic, 8)
     for (int i = 0; i < nx; ++i) {
-        const float x = origin[0] + (i + i_offset) * voxel_size;
         for (int j = 0; j < ny; ++j) {
+            const float x = origin[0] + (i + i_offset) * voxel_size;
             const float y = origin[1] + j * voxel_size;
             float *row = value + ((int64_t)i * ny + j) * nz;
             for (int k = 0; k < nz; ++k) {
@@ -143,6 +146,24 @@ void oracle_average_view_lut(const uint8_t *mask, const float *lut, int H, int W
             }
         }
     }
+}
+
+/* Thread control for the timed CPU baseline (bench.py reports the threads that were busy and the measured
+ * 1-thread -> all-thread speed-up).  The view functions parallelise over (plane, row) pairs, so a one-plane
+ * slab still spreads over every thread. */
+int oracle_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
 }
 
 const char *oracle_build_info(void) {

@@ -1,0 +1,33 @@
+// bp_kernels.h — launch wrappers of the kernels in bp_kernels.cu (the only translation unit with device code
+// for the back-projection path).  Not part of the C ABI.  Every wrapper only enqueues; callers check
+// cudaGetLastError() and count the launch.
+#ifndef BP_KERNELS_H
+#define BP_KERNELS_H
+#include <cuda_runtime.h>
+
+#include "bp_types.h"
+
+namespace bpk {
+
+// fused multi-view carve over the handle's planes (kernels/backprojection.c:57-84); CTA = 64 threads
+void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g);
+// fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
+void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g);
+// mask ingest: one view of any dtype / width -> 32x32-pixel bit tiles
+void pack_bits(cudaStream_t st, int dtype, const void *src, uint32_t *out, int H, int W, int tpr, int Hpad, uint32_t flags);
+// mask ingest, batched fast path (uint8, 16-byte aligned rows): every view of a chunk in one launch
+void pack_u8x16(dim3 grd, cudaStream_t st, uint32_t *pool, const PackJobs &jobs, uint32_t flags);
+// read-back helpers
+void expand_state(cudaStream_t st, const int8_t *state, int32_t *out, size_t n, int nz, int nzp, int v_carved, int v_seen,
+                  int v_unseen);
+void patch_rows(cudaStream_t st, const int8_t *state, const int8_t *snap, int32_t *host_out, size_t n_rows, int nz, int nzp,
+                int v_carved, int v_seen, int v_unseen, unsigned long long *count);
+void unpad_f32(cudaStream_t st, const float *in, float *out, size_t n, int nz, int nzp);
+void tail(cudaStream_t st, int n_blocks, bool carve, bool f64, const void *grid, void *out, size_t n, int nz, int nzp,
+          int v_carved, int v_seen, int v_unseen, int exp_clip, double *partial);
+void fill_f32(cudaStream_t st, float *p, size_t n, float v);
+// device self-test of the shared-reciprocal division (default stream)
+void selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches_d);
+
+}  // namespace bpk
+#endif  // BP_KERNELS_H

@@ -1,0 +1,361 @@
+// bp_process.cu — the host pipeline behind bp_process_views / bp_pack_views: view ordering, staging of host masks
+// (double-buffered H2D on a copy stream), mask ingest launches and the fused carve / average launches.
+// Replaces the per-view upload + launch + finish() loop of plant3dvision/cl.py:190-227, :282-303 of the reference.
+#include "bp_handle.h"
+#include "bp_geom.h"
+#include "bp_kernels.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <vector>
+
+namespace {
+using namespace bph;
+
+// BP_VIEW_RECT=1: copy (host masks) and pack only the rectangle of every view that the handle's planes project
+// into (view_rect).  Read at every call so that a test can switch it.  Off by default until measured.
+bool view_rect_enabled() {
+    const char *e = std::getenv("BP_VIEW_RECT");
+    return e && std::atoi(e) != 0;
+}
+
+// bit-pack ONE view whose raw mask already sits in device memory (general path: any dtype / width)
+int pack_view(bp_handle *h, uint32_t *pool, const void *src, int H, int W, int dtype, uint32_t flags, size_t off,
+              const TiledDims &d) {
+    bpk::pack_bits(h->stream, dtype, src, pool + off, H, W, d.tpr, d.tiles_y * 32, flags);
+    CU(cudaGetLastError());
+    h->launches++;
+    return BP_OK;
+}
+
+// Carving is order-independent (kernels/backprojection.c:65-83: carved is absorbing, seen is
+// set once), so the fused kernel is free to visit the views of a batch in any order.  Visiting
+// them in farthest-point order of their optical axes (r6 r7 r8; a view and its antipode count
+// as the same direction, their silhouettes nearly coincide) carves most of the empty space in
+// the first handful of views, after which whole warps leave the view loop.  Averaging keeps the
+// caller's order: its float32 sum is order-dependent (cl.py:223-226 accumulates view by view).
+void spread_order(const float *cams, int n, std::vector<int> &order) {
+    order.resize(n);
+    if (n == 0) return;
+    std::vector<float> far(n, 2.0f);  // min over chosen of (1 - |cos|); 2 = nothing chosen yet
+    std::vector<char> used(n, 0);
+    int cur = 0;
+    for (int q = 0; q < n; ++q) {
+        order[q] = cur;
+        used[cur] = 1;
+        const float *a = cams + 16 * (size_t)cur + 10;
+        const float na = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+        int best = -1;
+        float best_d = -1.0f;
+        for (int v = 0; v < n; ++v) {
+            if (used[v]) continue;
+            const float *b = cams + 16 * (size_t)v + 10;
+            const float nb = std::sqrt(b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
+            float c = (a[0] * b[0] + a[1] * b[1] + a[2] * b[2]) / (na * nb);
+            if (!(c == c)) c = 1.0f;
+            const float d = 1.0f - std::fabs(c);
+            if (d < far[v]) far[v] = d;
+            if (far[v] > best_d) {
+                best_d = far[v];
+                best = v;
+            }
+        }
+        cur = best;
+    }
+}
+
+int check_views_args(bp_handle *h, int dtype, uint32_t flags, const float *lut) {
+    if (elem_size(dtype) == 0) return bp_fail(BP_EINVAL, "unknown mask_dtype %d", dtype);
+    if (h->mode == BP_MODE_AVERAGING) {
+        if (dtype != BP_MASK_U8 && dtype != BP_MASK_F32)
+            return bp_fail(BP_EINVAL, "averaging takes U8 (+lut) or F32 maps; convert other types on the host");
+        if (dtype == BP_MASK_U8 && !lut) return bp_fail(BP_EINVAL, "averaging with a U8 map needs a 256-entry lut");
+        if (dtype == BP_MASK_F32 && (flags & (BP_FLAG_INVERT | BP_FLAG_BOOL_INVERT)))
+            return bp_fail(BP_EINVAL, "invert is not defined for float maps (np.invert raises)");
+    } else if (dtype == BP_MASK_F32 && (flags & (BP_FLAG_INVERT | BP_FLAG_BOOL_INVERT))) {
+        return bp_fail(BP_EINVAL, "invert is not defined for float masks (np.invert raises)");
+    }
+    return BP_OK;
+}
+
+}  // namespace
+
+namespace bph {
+
+// Shared body of bp_process_views and bp_pack_views.  pack_dst != NULL: ingest only (upload + bit-pack,
+// view q at pack_dst + q * pack_stride, caller's order, no carve launch).
+int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *masks, const int32_t *hw, int mask_dtype,
+                 uint32_t flags, const float *lut, void *pack_dst, int64_t pack_stride) {
+    if (!h) return bp_fail(BP_EINVAL, "null handle");
+    if (n < 0) return bp_fail(BP_EINVAL, "negative view count");
+    if (n == 0) return BP_OK;
+    const bool pack_only = pack_dst != nullptr;
+    if ((!cams && !pack_only) || !masks || !hw) return bp_fail(BP_EINVAL, "null argument");
+    int rc = check_views_args(h, mask_dtype, flags, lut);
+    if (rc) return rc;
+    const bool carving = h->mode == BP_MODE_CARVING;
+    const bool packed_in = (flags & BP_FLAG_PACKED_MASKS) != 0;
+    if ((pack_only || packed_in) && !carving) return bp_fail(BP_ESTATE, "bit-packed masks belong to carving handles");
+    if (pack_only && packed_in) return bp_fail(BP_EINVAL, "masks are already packed");
+    if (packed_in) flags |= BP_FLAG_DEVICE_MASKS;
+    size_t max_raw = 0;
+    for (int v = 0; v < n; ++v) {
+        if (!masks[v]) return bp_fail(BP_EINVAL, "mask %d is null", v);
+        if (hw[2 * v] <= 0 || hw[2 * v + 1] <= 0 || hw[2 * v] >= (1 << 24) || hw[2 * v + 1] >= (1 << 24))
+            return bp_fail(BP_EINVAL, "mask %d has bad size %d x %d", v, hw[2 * v], hw[2 * v + 1]);
+        if (carving && (size_t)hw[2 * v] * (size_t)hw[2 * v + 1] >= ((size_t)1 << 35))
+            return bp_fail(BP_EINVAL, "mask %d is too large (%d x %d): tile word offsets are 32-bit", v, hw[2 * v], hw[2 * v + 1]);
+        if (!carving && (size_t)hw[2 * v] * (size_t)hw[2 * v + 1] >= ((size_t)1 << 31))
+            return bp_fail(BP_EINVAL, "map %d is too large (%d x %d): element offsets are 32-bit", v, hw[2 * v], hw[2 * v + 1]);
+        const size_t raw = ((size_t)hw[2 * v] * hw[2 * v + 1] * elem_size(mask_dtype) + 255) & ~(size_t)255;
+        if (raw > max_raw) max_raw = raw;
+    }
+    CU(cudaSetDevice(h->device));
+    if (!pack_only && (h->g.ni == 0 || h->g.ny == 0 || h->g.nz == 0)) return BP_OK;  // empty grid: nothing to do
+    if (!carving && mask_dtype == BP_MASK_U8) {
+        // np.invert on the map (cl.py:300-301) == the same bytes read through a permuted table
+        for (int b = 0; b < 256; ++b) {
+            int src = b;
+            if (flags & BP_FLAG_BOOL_INVERT) src = (b == 0) ? 1 : 0;
+            else if (flags & BP_FLAG_INVERT) src = 255 - b;
+            h->lut_h[b] = lut[src];
+        }
+        CU(cudaMemcpyAsync(h->lut_d, h->lut_h, 256 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    }
+    if (h->ev_kernel.size() > 2048) {
+        rc = fold_events(h);
+        if (rc) return rc;
+    }
+    const bool host_masks = !(flags & BP_FLAG_DEVICE_MASKS);
+
+    // visiting order (carving only; see spread_order) and chunking.  Device-resident masks go
+    // kMaxViews at a time; host masks in chunks that fit a staging buffer, so that the H2D copy
+    // of chunk c+1 (copy stream) overlaps the pack + carve/average of chunk c (main stream).
+    std::vector<int> order;
+    if (carving && !pack_only) {
+        spread_order(cams, n, order);
+    } else {
+        order.resize(n);
+        for (int v = 0; v < n; ++v) order[v] = v;
+    }
+    int chunk = kMaxViews;
+    if (host_masks) {
+        size_t stage_bytes = kStageBytes;  // BP_STAGE_BYTES: smaller chunks, for tests of the chunk pipeline
+        if (const char *e = std::getenv("BP_STAGE_BYTES")) {
+            const long long v = std::atoll(e);
+            if (v > 0) stage_bytes = (size_t)v;
+        }
+        const size_t per = stage_bytes / max_raw;
+        chunk = (int)(per < 1 ? 1 : (per > (size_t)kMaxViews ? (size_t)kMaxViews : per));
+        const int n_chunks = (n + chunk - 1) / chunk;
+        for (int s = 0; s < (n_chunks > 1 ? 2 : 1); ++s) {
+            const size_t want = max_raw * (size_t)(chunk < n ? chunk : n);
+            if (h->stage_bytes[s] < want) {
+                CU(cudaStreamSynchronize(h->stream));
+                CU(cudaStreamSynchronize(h->cstream));
+                if (h->stage[s]) CU(cudaFree(h->stage[s]));
+                h->stage[s] = nullptr;
+                h->stage_bytes[s] = 0;
+                cudaError_t e = cudaMalloc(&h->stage[s], want);
+                if (e != cudaSuccess)
+                    return bp_fail(BP_ENOMEM, "cudaMalloc(%zu) for mask staging failed: %s", want, cudaGetErrorString(e));
+                h->stage_bytes[s] = want;
+            }
+        }
+    }
+
+    static thread_local Batch batch;     // 22.5 KB, filled per launch
+    static thread_local PackJobs jobs;   // 12 KB
+    std::vector<TiledDims> dims;
+    std::vector<const void *> src;
+    // BP_VIEW_RECT: per view, the rectangle the handle's planes project into; only that part of a mask is copied
+    // (host masks) and packed.  Views that go through the general packer (pack_view) keep the whole image.
+    // Packing for other ranks (bp_pack_views_cams): the tiles go to every GPU, so the rectangle is the WHOLE grid's.
+    const bool use_rect = view_rect_enabled() && cams && !packed_in && (pack_only || h->g.ni > 0);
+    const int rect_i_lo = (use_rect && !pack_only) ? global_plane_host(h->g, 0) : 0;
+    const int rect_i_hi = !use_rect ? 0 : pack_only ? h->shape[0] - 1 : global_plane_host(h->g, h->g.ni - 1);
+    std::vector<ViewRect> rects;
+    auto rect_of = [&](int v) {
+        const int H = hw[2 * v], W = hw[2 * v + 1];
+        const ViewRect whole = {0, 0, W, H};
+        // carving: only the batched uint8 packer knows about rectangles (staged copies are 256-byte aligned)
+        const bool can = use_rect && (!carving || (mask_dtype == BP_MASK_U8 && (W % 16) == 0 &&
+                                                   (host_masks || ((uintptr_t)masks[v] % 16) == 0)));
+        return can ? bp_box_rect(rect_i_lo, rect_i_hi, 0, h->g.ny - 1, 0, h->g.nz - 1, h->g.ox, h->g.oy, h->g.oz, h->g.vs,
+                                 cams + 16 * (size_t)v, H, W)
+                   : whole;
+    };
+    // Speculative read-back (bp_set_readback_target): take the early copy of the volume after the chunk that leaves
+    // about as much upload time as the read-back needs (both cross PCIe, in opposite directions), but not before
+    // the first 16 views (farthest-point order) have removed the bulk of the empty space.
+    int ci_snap = -1;
+    if (carving && host_masks && !pack_only && h->spec_target && chunk < n) {
+        const int n_chunks = (n + chunk - 1) / chunk;
+        double h2d = 0.0;
+        for (int v = 0; v < n; ++v) {
+            const ViewRect R = rect_of(v);
+            h2d += (double)(R.x1 - R.x0) * (double)(R.y1 - R.y0) * (double)elem_size(mask_dtype);
+        }
+        const double d2h = 4.0 * (double)h->g.ni * h->g.ny * h->g.nz;
+        double frac = h2d > 0.0 ? 1.0 - d2h / h2d : 0.0;
+        if (const char *e = std::getenv("BP_SPEC_AT")) frac = std::atof(e);  // experiments: fraction of the views
+        int before = (int)std::ceil(frac * n);
+        if (before < 16) before = 16;
+        const int ci = (before + chunk - 1) / chunk - 1;  // the chunk whose carve launch sees view number `before`
+        if (ci < n_chunks - 1) ci_snap = ci;                  // else nothing would be left to hide the copy behind
+    }
+    int ci = 0;
+    for (int v0 = 0; v0 < n; v0 += chunk, ++ci) {
+        const int nb = (n - v0 < chunk) ? (n - v0) : chunk;
+        const int s = ci & 1;
+        dims.resize(nb);
+        src.resize(nb);
+        rects.resize(nb);
+        for (int q = 0; q < nb; ++q) rects[q] = rect_of(order[v0 + q]);
+        if (carving) {
+            size_t total = 0;
+            for (int q = 0; q < nb; ++q) {
+                const int v = order[v0 + q];
+                dims[q] = tiled_dims(hw[2 * v], hw[2 * v + 1]);
+                total += dims[q].elems;
+                if (pack_only && (int64_t)(dims[q].elems * 4) > pack_stride)
+                    return bp_fail(BP_EINVAL, "view_stride %lld is smaller than the %zu bytes view %d packs to",
+                                (long long)pack_stride, dims[q].elems * 4, v);
+            }
+            if (!pack_only && !packed_in) {
+                rc = ensure(&h->pool, &h->pool_bytes, total * 4, h->stream);
+                if (rc) return rc;
+            }
+        }
+        uint32_t *const pool_base = pack_only ? (uint32_t *)pack_dst : (uint32_t *)h->pool;
+        if (host_masks) {
+            // the staging buffer is free once the work of the chunk that used it last has run
+            CU(cudaStreamWaitEvent(h->cstream, h->ev_stage_free[s], 0));
+            size_t so = 0;
+            for (int q = 0; q < nb; ++q) {
+                const int v = order[v0 + q];
+                const size_t es = elem_size(mask_dtype);
+                const size_t raw = (size_t)hw[2 * v] * hw[2 * v + 1] * es;
+                char *dst = (char *)h->stage[s] + so;
+                const ViewRect &R = rects[q];
+                const size_t Wq = (size_t)hw[2 * v + 1];
+                const size_t first = ((size_t)R.y0 * Wq + (size_t)R.x0) * es;  // same layout, rows / columns left out
+                if (R.x0 == 0 && (size_t)R.x1 == Wq) {
+                    const size_t nbytes = (size_t)(R.y1 - R.y0) * Wq * es;
+                    CU(cudaMemcpyAsync(dst + first, (const char *)masks[v] + first, nbytes, cudaMemcpyHostToDevice, h->cstream));
+                    h->h2d_bytes += (int64_t)nbytes;
+                } else {
+                    CU(cudaMemcpy2DAsync(dst + first, Wq * es, (const char *)masks[v] + first, Wq * es,
+                                         (size_t)(R.x1 - R.x0) * es, (size_t)(R.y1 - R.y0), cudaMemcpyHostToDevice, h->cstream));
+                    h->h2d_bytes += (int64_t)((size_t)(R.x1 - R.x0) * es * (size_t)(R.y1 - R.y0));
+                }
+                src[q] = dst;
+                so += (raw + 255) & ~(size_t)255;
+            }
+            CU(cudaEventRecord(h->ev_copied[s], h->cstream));
+            CU(cudaStreamWaitEvent(h->stream, h->ev_copied[s], 0));
+        } else {
+            for (int q = 0; q < nb; ++q) src[q] = masks[order[v0 + q]];
+        }
+        cudaEvent_t i0, i1, k0 = nullptr, k1 = nullptr;
+        if ((rc = get_event(h, &i0)) || (rc = get_event(h, &i1))) return rc;
+        if (!pack_only && ((rc = get_event(h, &k0)) || (rc = get_event(h, &k1)))) return rc;
+        CU(cudaEventRecord(i0, h->stream));
+        size_t off = 0;
+        batch.n = nb;
+        {   // the fast division path assumes no intermediate can overflow (see DivGuard)
+            auto tame = [](float f) { return std::fabs(f) < 0x1p40f; };  // false for NaN / Inf too
+            const GridInfo &G = h->g;
+            const float ext[3] = {(float)h->shape[0] * G.vs, (float)G.ny * G.vs, (float)G.nz * G.vs};
+            bool all = tame(G.ox) && tame(G.oy) && tame(G.oz) && tame(G.vs) && tame(ext[0]) && tame(ext[1]) && tame(ext[2]);
+            for (int q = 0; q < nb && all && !pack_only; ++q)
+                for (int a = 0; a < 16; ++a) all = all && tame(cams[16 * (size_t)order[v0 + q] + a]);
+            batch.force_exact = all ? 0 : 1;
+        }
+        jobs.n = 0;
+        int jw = 0, jt = 0;
+        for (int q = 0; q < nb; ++q) {
+            const int v = order[v0 + q];
+            const int H = hw[2 * v], W = hw[2 * v + 1];
+            ViewParams &P = batch.v[q];
+            if (pack_only) off = (size_t)(v0 + q) * (size_t)(pack_stride / 4);
+            if (packed_in) {
+                P.pitch = (uint32_t)dims[q].tpr;
+                P.map = src[q];
+            } else if (carving) {
+                const bool fast = mask_dtype == BP_MASK_U8 && (W % 16) == 0 && ((uintptr_t)src[q] % 16) == 0;
+                if (fast) {
+                    PackJob &J = jobs.j[jobs.n++];
+                    J.src = src[q];
+                    J.off = off;
+                    J.H = H;
+                    J.W = W;
+                    J.tpr = dims[q].tpr;
+                    const ViewRect &R = rects[q];
+                    J.ty0 = R.y0 >> 5;
+                    J.ty1 = (R.y1 + 31) >> 5;
+                    J.px0 = R.x0;
+                    J.px1 = R.x1;
+                    J.pad = 0;
+                    const int segs = ((R.x1 + 511) >> 9) - (R.x0 >> 9);  // 512-pixel segments = CTAs along x
+                    if (segs > jw) jw = segs;
+                    if (J.ty1 - J.ty0 > jt) jt = J.ty1 - J.ty0;
+                } else {
+                    rc = pack_view(h, pool_base, src[q], H, W, mask_dtype, flags, off, dims[q]);
+                    if (rc) return rc;
+                }
+                P.pitch = (uint32_t)dims[q].tpr;
+                P.map = pool_base + off;
+                off += dims[q].elems;
+            } else {
+                // averaging reads the caller's row-major map in place (device masks) or its staged copy
+                P.pitch = (uint32_t)W;
+                P.map = src[q];
+            }
+            if (pack_only) continue;
+            const float *c = cams + 16 * (size_t)v;
+            P.fx = c[0]; P.fy = c[1]; P.cx = c[2]; P.cy = c[3];
+            for (int a = 0; a < 9; ++a) P.r[a] = c[4 + a];
+            for (int a = 0; a < 3; ++a) P.t[a] = c[13 + a];
+            P.Wf = (float)W;
+            P.Hf = (float)H;
+            P.Wi = (uint32_t)W;
+            P.Hi = (uint32_t)H;
+            P.pad = 0;
+        }
+        if (jobs.n > 0) {
+            dim3 grd(jw, jt, jobs.n);
+            bpk::pack_u8x16(grd, h->stream, pool_base, jobs, flags);
+            CU(cudaGetLastError());
+            h->launches++;
+        }
+        CU(cudaEventRecord(i1, h->stream));
+        h->ev_ingest.emplace_back(i0, i1);
+        if (host_masks && carving) CU(cudaEventRecord(h->ev_stage_free[s], h->stream));
+        if (pack_only) continue;
+        CU(cudaEventRecord(k0, h->stream));
+        const dim3 grd = h->launch_grid;
+        if (carving) {
+            // (pageable source: the call returns once the bytes are staged, so `batch` may be reused)
+            CU(cudaMemcpyAsync(h->views_d[0], batch.v, sizeof(ViewParams) * (size_t)batch.n, cudaMemcpyHostToDevice, h->stream));
+            bpk::carve(grd, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g);
+        } else {
+            bpk::average(grd, h->stream, mask_dtype == BP_MASK_U8, (float *)h->grid, h->lut_d, batch, h->g);
+        }
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(k1, h->stream));
+        h->ev_kernel.emplace_back(k0, k1);
+        h->launches++;
+        if (host_masks && !carving) CU(cudaEventRecord(h->ev_stage_free[s], h->stream));
+        if (ci == ci_snap) {
+            rc = start_spec_readback(h);
+            if (rc) return rc;
+        }
+    }
+    // host masks are never retained: every H2D copy has completed when this returns
+    if (host_masks) CU(cudaStreamSynchronize(h->cstream));
+    return BP_OK;
+}
+
+}  // namespace bph

@@ -60,8 +60,16 @@ def test_library_exports_every_declared_symbol():
     for name in declared_functions() + declared_functions(V2P_HEADER) + declared_functions(MASKS_HEADER):
         assert hasattr(lib, name), f"libbp_b200.so does not export {name}"
     # and nothing C++-mangled leaks an unintended bp_* entry point
-    assert lib.bp_version().decode().startswith("bp_b200 ")
-    assert lib.bp_version().decode().endswith("sm_100a")
+    import re
+    # "bp_b200 <version> sm_100a src=<hash of every source file> kern=<hash of the device code>"
+    assert re.fullmatch(r"bp_b200 [0-9.]+ sm_100a src=[0-9a-f]{16} kern=[0-9a-f]{16}", lib.bp_version().decode())
+
+
+def test_built_library_carries_the_hash_of_the_sources_in_the_tree():
+    """build() rebuilds on a content hash, not on mtime (a stale binary must never be benchmarked): the hash embedded
+    in the library is the hash of the sources next to it."""
+    import __graft_entry__ as g
+    assert g.built_hashes() == g.source_hashes()
 
 
 def test_header_cites_the_reference_interface_it_replaces():

@@ -19,7 +19,7 @@ BP_VIEW_RECT=1 python bench.py > gpurun_out/bench_view_rect.json 2> gpurun_out/b
 BP_SPEC_READBACK=1 python bench.py --no-averaging --no-cpu > gpurun_out/bench_spec.json 2> gpurun_out/bench_spec.err; echo "bench (spec) rc=$?"
 BP_SPEC_READBACK=1 BP_VIEW_RECT=1 python bench.py --no-averaging --no-cpu > gpurun_out/bench_spec_rect.json 2> gpurun_out/bench_spec_rect.err; echo "bench (spec+rect) rc=$?"
 for tool in memcheck racecheck initcheck; do
-  timeout 600 compute-sanitizer --tool $tool --error-exitcode 9 python __graft_entry__.py smoke \
+  timeout 400 compute-sanitizer --tool $tool --error-exitcode 9 python __graft_entry__.py smoke \
     > gpurun_out/sanitizer_$tool.log 2>&1
   echo "compute-sanitizer $tool rc=$?" | tee -a gpurun_out/sanitizer_$tool.log
   tail -4 gpurun_out/sanitizer_$tool.log
