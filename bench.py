@@ -412,9 +412,18 @@ def measure_mode(args, mode, w, cams, masks_np, ptrs, hw, views_host, world, ran
                          f"oracle/bp_oracle.c, OpenMP over {cores} threads",
                "sample_matches_gpu": ok}
 
+    work = None
+    if mode == "carving" and hasattr(eng, "work_stats"):
+        step_resident()
+        eng.sync()
+        eng.work_stats()  # reset the counter, then count exactly one step
+        step_resident()
+        ev, blocks, dead = eng.work_stats()
+        work = {"nominal_voxel_views": float(len(eng.planes)) * ny * nz * n_views, "evaluated_voxel_views": ev or None,
+                "cull_blocks": blocks, "cull_blocks_dead": dead}
     bp.close()
     return {"value": value, "ms_per_step": ms_step, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
-            "gpu_launches": int(tsum[3]), "clocks": clk}
+            "gpu_launches": int(tsum[3]), "clocks": clk, "work": work}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -472,6 +481,7 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "f32 projection, i8 state" if args.mode == "carving" else "f32",
             "data": "synthetic", "config": workload_config(w, args, world),
             "e2e": e2e, "gpu_launches": launches_total, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "work": m["work"],
         }
         if other is not None:
             line["averaging"] = other

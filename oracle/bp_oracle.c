@@ -148,6 +148,32 @@ void oracle_average_view_lut(const uint8_t *mask, const float *lut, int H, int W
     }
 }
 
+/* Projection alone (kernels/backprojection.c:3-34) of every voxel of the grid into one view: hit[idx] = 1 and
+ * (px[idx], py[idx]) = the pixel when the voxel lands inside the W x H image, else hit[idx] = 0.  Used by the tests of
+ * the conservative pixel bounds behind the view rectangles and the block cull (csrc/bp_geom.h). */
+void oracle_project_view(int H, int W, int32_t *px, int32_t *py, uint8_t *hit,
+                         const float *intr, const float *rot, const float *tvec,
+                         const float *origin, float voxel_size, const int32_t *shape, int i_offset) {
+    const bp_cam c = load_cam(intr, rot, tvec);
+    const int nx = shape[0], ny = shape[1], nz = shape[2];
+#pragma omp parallel for collapse(2) schedule(static)
+    for (int i = 0; i < nx; ++i) {
+        for (int j = 0; j < ny; ++j) {
+            const float x = origin[0] + (i + i_offset) * voxel_size;
+            const float y = origin[1] + j * voxel_size;
+            const int64_t base = ((int64_t)i * ny + j) * nz;
+            for (int k = 0; k < nz; ++k) {
+                const float z = origin[2] + k * voxel_size;
+                int ix = 0, iy = 0;
+                const int ok = project(&c, x, y, z, W, H, &ix, &iy);
+                hit[base + k] = (uint8_t)ok;
+                px[base + k] = ok ? ix : -1;
+                py[base + k] = ok ? iy : -1;
+            }
+        }
+    }
+}
+
 /* Thread control for the timed CPU baseline (bench.py reports the threads that were busy and the measured
  * 1-thread -> all-thread speed-up).  The view functions parallelise over (plane, row) pairs, so a one-plane
  * slab still spreads over every thread. */

@@ -20,6 +20,7 @@ SYMBOLS = [
     "bp_get_values", "bp_get_values_tail", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
     "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect", "bp_pack_views_cams", "bp_set_readback_target", "bp_spec_stats",
+    "bp_work_stats", "bp_box_bounds_host",
 ]
 
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
@@ -79,9 +80,13 @@ def lib():
                                            ctypes.POINTER(ctypes.c_uint64)]
         L.bp_set_readback_target.argtypes = [vp, vp]
         L.bp_spec_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
+        L.bp_work_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64),
+                                    ctypes.POINTER(ctypes.c_int64)]
         L.bp_ingest_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_int64)]
         L.bp_view_rect.argtypes = [c_i, ctypes.c_int32, ctypes.c_int32, c_f, ctypes.c_float, c_f, ctypes.c_int32,
                                    ctypes.c_int32, c_i]
+        L.bp_box_bounds_host.argtypes = [c_i, c_f, ctypes.c_float, c_f, ctypes.c_int32, ctypes.c_int32,
+                                         ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), c_i]
         L.bp_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.bp_host_free.argtypes = [vp]
         c_d = ctypes.POINTER(ctypes.c_double)

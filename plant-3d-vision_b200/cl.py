@@ -551,6 +551,13 @@ class Backprojection(object):
         _cabi.check(_cabi.lib().bp_timing(self._handle(), ctypes.byref(k), ctypes.byref(g), ctypes.byref(n)))
         return k.value, g.value, n.value
 
+    def work_stats(self):
+        """(projections evaluated, cull blocks, cull blocks written off as carved): diagnostics of the carve path
+        (bp_work_stats; the first is counted only under ``BP_COUNT_WORK=1``)."""
+        a, b, c = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()
+        _cabi.check(_cabi.lib().bp_work_stats(self._handle(), ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return a.value, b.value, c.value
+
     def ingest_bytes(self):
         """Mask bytes copied host -> device on this handle since creation (see bp_ingest_bytes)."""
         n = ctypes.c_int64()

@@ -40,6 +40,18 @@ struct bp_handle {
     float kernel_ms = 0.f, ingest_ms = 0.f;
     int64_t launches = 0;
     int64_t h2d_bytes = 0;  // mask bytes copied host -> device since creation (bp_ingest_bytes)
+    // block cull of the carve path (bp_kernels.cu: cull_blocks_kernel / carve_items_kernel); NULL when the handle is not
+    // a carving handle or its block grid does not fit the 16-bit block coordinates of the work list
+    CullGrid cg{};
+    uint8_t *blk_dead = nullptr;        // one byte per cull block, persistent until bp_clear
+    uint2 *blk_live = nullptr;          // work list of one launch
+    uint32_t *cull_counters = nullptr;  // {live blocks, next work item, blocks killed, -}
+    CullView *cull_views_d = nullptr;   // kCullViews entries
+    void *sat_pool = nullptr;           // summed-area tables (+ scratch) of one launch
+    size_t sat_bytes = 0;
+    int items_ctas = 0;                 // persistent grid of carve_items_kernel
+    bool count_work = false;            // BP_COUNT_WORK=1: count the projections the carve kernels evaluate
+    unsigned long long *work_d = nullptr;
     // speculative read-back (bp_set_readback_target; carving, host masks in several chunks)
     void *spec_target = nullptr;      // pinned host volume the next bp_get_values will be given
     void *spec_target_dev = nullptr;  // the same memory as the device addresses it

@@ -9,8 +9,20 @@
 
 namespace bpk {
 
-// fused multi-view carve over the handle's planes (kernels/backprojection.c:57-84); CTA = 64 threads
-void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g);
+// fused multi-view carve over EVERY patch of the handle's planes (kernels/backprojection.c:57-84); CTA = 64 threads.
+// work_total != NULL: the counting variant (adds the projections evaluated; diagnostics only)
+void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
+           unsigned long long *work_total);
+// block cull of the carve path: summed-area tables of "tile has a foreground bit" for the views of `jobs`
+// (two launches), the cull itself (dead flags, zero fill of the blocks it kills, work list of the survivors;
+// counters = {live blocks, next work item, blocks killed}, zeroed by the caller), and the persistent kernel that
+// carves the patches of the surviving blocks (n_ctas = SM count x carve_items_ctas_per_sm()).
+void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
+void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
+                 uint8_t *dead, uint2 *live, uint32_t *counters);
+int carve_items_ctas_per_sm();
+void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
+                 const uint2 *live, uint32_t *counters, unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
 void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g);
 // mask ingest: one view of any dtype / width -> 32x32-pixel bit tiles

@@ -20,6 +20,22 @@ bool view_rect_enabled() {
     return e && std::atoi(e) != 0;
 }
 
+// BP_CARVE_CULL=0 switches the block cull off: every launch then sweeps every patch of the grid with carve_kernel
+// (the round-1 path; kept for A/B measurements and as the path for non-finite / huge parameters).  Default on.
+bool carve_cull_enabled() {
+    const char *e = std::getenv("BP_CARVE_CULL");
+    return !e || std::atoi(e) != 0;
+}
+
+// Two-tier masks (device-resident uint8 masks only): the first BP_PACK_HEAD views of a launch, in visiting order, are
+// bit-packed; the later ones are read in place by the few voxels that survive the first (see bp_kernels.cu).
+// Negative = pack every view.  Default 32: measured on C5.
+int pack_head_views() {
+    const char *e = std::getenv("BP_PACK_HEAD");
+    const int v = e ? std::atoi(e) : 32;
+    return v < 0 ? kMaxViews : v;
+}
+
 // bit-pack ONE view whose raw mask already sits in device memory (general path: any dtype / width)
 int pack_view(bp_handle *h, uint32_t *pool, const void *src, int H, int W, int dtype, uint32_t flags, size_t off,
               const TiledDims &d) {
@@ -76,6 +92,62 @@ int check_views_args(bp_handle *h, int dtype, uint32_t flags, const float *lut) 
     } else if (dtype == BP_MASK_F32 && (flags & (BP_FLAG_INVERT | BP_FLAG_BOOL_INVERT))) {
         return bp_fail(BP_EINVAL, "invert is not defined for float masks (np.invert raises)");
     }
+    return BP_OK;
+}
+
+
+// One carving launch through the block cull (bp_kernels.cu): summed-area tables of the first bit-packed views, the cull
+// (persistent dead flags, zero fill of the blocks it kills, work list of the survivors) and the persistent kernel that
+// carves the patches of the surviving blocks.  `order` = this launch's views as indices into hw / cams.
+int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const int *order, const float *cams,
+                      unsigned long long *work) {
+    static thread_local SatJobs sat;
+    static thread_local CullView cv[kCullViews];
+    int n_cull = 0;
+    while (n_cull < batch.n && n_cull < kCullViews && batch.v[n_cull].kind == 0) ++n_cull;  // the packed head
+    size_t need = 0;
+    int max_tiles = 0;
+    for (int q = 0; q < n_cull; ++q) {
+        const int v = order[q];
+        const TiledDims d = tiled_dims(hw[2 * v], hw[2 * v + 1]);
+        need += (((size_t)(d.tiles_y + 1) * (d.tpr + 1) * 4 + 255) & ~(size_t)255) + (((size_t)d.tiles_y * d.tpr + 255) & ~(size_t)255);
+        if (d.tpr * d.tiles_y > max_tiles) max_tiles = d.tpr * d.tiles_y;
+    }
+    int rc = ensure(&h->sat_pool, &h->sat_bytes, need, h->stream);
+    if (rc) return rc;
+    char *pool = (char *)h->sat_pool;
+    sat.n = n_cull;
+    for (int q = 0; q < n_cull; ++q) {
+        const int v = order[q];
+        const TiledDims d = tiled_dims(hw[2 * v], hw[2 * v + 1]);
+        SatJob &J = sat.j[q];
+        J.tiles = (const uint32_t *)batch.v[q].map;
+        J.sat = (uint32_t *)pool;
+        pool += ((size_t)(d.tiles_y + 1) * (d.tpr + 1) * 4 + 255) & ~(size_t)255;
+        J.any = (uint8_t *)pool;
+        pool += ((size_t)d.tiles_y * d.tpr + 255) & ~(size_t)255;
+        J.tpr = d.tpr;
+        J.tiles_y = d.tiles_y;
+        CullView &V = cv[q];
+        for (int a = 0; a < 16; ++a) V.cam[a] = cams[16 * (size_t)v + a];
+        V.sat = J.sat;
+        V.tpr1 = d.tpr + 1;
+        V.W = hw[2 * v + 1];
+        V.H = hw[2 * v];
+        V.pad[0] = V.pad[1] = V.pad[2] = 0;
+    }
+    if (n_cull > 0) {
+        bpk::tile_sat(h->stream, sat, max_tiles);
+        CU(cudaGetLastError());
+        h->launches += 2;
+        CU(cudaMemcpyAsync(h->cull_views_d, cv, sizeof(CullView) * (size_t)n_cull, cudaMemcpyHostToDevice, h->stream));
+    }
+    CU(cudaMemsetAsync(h->cull_counters, 0, 4 * sizeof(uint32_t), h->stream));
+    bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, h->blk_dead, h->blk_live, h->cull_counters);
+    CU(cudaGetLastError());
+    bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
+                     h->cull_counters, work);
+    h->launches += 1;  // (the caller counts the carve launch itself)
     return BP_OK;
 }
 
@@ -169,6 +241,7 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
     static thread_local PackJobs jobs;   // 12 KB
     std::vector<TiledDims> dims;
     std::vector<const void *> src;
+    std::vector<char> raw_view;
     // BP_VIEW_RECT: per view, the rectangle the handle's planes project into; only that part of a mask is copied
     // (host masks) and packed.  Views that go through the general packer (pack_view) keep the whole image.
     // Packing for other ranks (bp_pack_views_cams): the tiles go to every GPU, so the rectangle is the WHOLE grid's.
@@ -213,12 +286,21 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
         src.resize(nb);
         rects.resize(nb);
         for (int q = 0; q < nb; ++q) rects[q] = rect_of(order[v0 + q]);
+        // two-tier masks: which views of this launch are read raw (device-resident uint8 masks past the packed head)
+        raw_view.assign(nb, 0);
+        if (carving && !pack_only && !packed_in && !host_masks && mask_dtype == BP_MASK_U8) {
+            const int head = pack_head_views();
+            for (int q = head; q < nb; ++q) {
+                const int v = order[v0 + q];
+                raw_view[q] = ((size_t)hw[2 * v] * (size_t)hw[2 * v + 1] < ((size_t)1 << 32)) ? 1 : 0;  // 32-bit byte offsets
+            }
+        }
         if (carving) {
             size_t total = 0;
             for (int q = 0; q < nb; ++q) {
                 const int v = order[v0 + q];
                 dims[q] = tiled_dims(hw[2 * v], hw[2 * v + 1]);
-                total += dims[q].elems;
+                if (!raw_view[q]) total += dims[q].elems;
                 if (pack_only && (int64_t)(dims[q].elems * 4) > pack_stride)
                     return bp_fail(BP_EINVAL, "view_stride %lld is smaller than the %zu bytes view %d packs to",
                                 (long long)pack_stride, dims[q].elems * 4, v);
@@ -280,9 +362,14 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
             const int H = hw[2 * v], W = hw[2 * v + 1];
             ViewParams &P = batch.v[q];
             if (pack_only) off = (size_t)(v0 + q) * (size_t)(pack_stride / 4);
+            P.kind = 0;
             if (packed_in) {
                 P.pitch = (uint32_t)dims[q].tpr;
                 P.map = src[q];
+            } else if (carving && raw_view[q]) {
+                P.pitch = (uint32_t)W;
+                P.map = src[q];
+                P.kind = raw_view_kind(flags);
             } else if (carving) {
                 const bool fast = mask_dtype == BP_MASK_U8 && (W % 16) == 0 && ((uintptr_t)src[q] % 16) == 0;
                 if (fast) {
@@ -322,7 +409,6 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
             P.Hf = (float)H;
             P.Wi = (uint32_t)W;
             P.Hi = (uint32_t)H;
-            P.pad = 0;
         }
         if (jobs.n > 0) {
             dim3 grd(jw, jt, jobs.n);
@@ -339,7 +425,13 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
         if (carving) {
             // (pageable source: the call returns once the bytes are staged, so `batch` may be reused)
             CU(cudaMemcpyAsync(h->views_d[0], batch.v, sizeof(ViewParams) * (size_t)batch.n, cudaMemcpyHostToDevice, h->stream));
-            bpk::carve(grd, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g);
+            unsigned long long *work = h->count_work ? h->work_d : nullptr;
+            if (h->blk_dead && !batch.force_exact && carve_cull_enabled()) {
+                rc = launch_cull_carve(h, batch, hw, order.data() + v0, cams, work);
+                if (rc) return rc;
+            } else {
+                bpk::carve(grd, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, work);
+            }
         } else {
             bpk::average(grd, h->stream, mask_dtype == BP_MASK_U8, (float *)h->grid, h->lut_d, batch, h->g);
         }

@@ -17,10 +17,21 @@ struct ViewParams {  // 96 bytes
     float Wf, Hf;           // image width / height as floats (exact below 2^24)
     uint32_t pitch;         // carving: 32x32-pixel bit tiles per tile row; averaging: elements per row
     uint32_t Wi, Hi;        // the same width / height as integers
-    uint32_t pad;
-    const void *map;        // carving: this view's bit tiles; averaging: row-major uint8 / float32 map
+    uint32_t kind;          // carving: 0 = bit tiles; else a RAW row-major uint8 mask read in place (kViewRaw...)
+    const void *map;        // carving: this view's bit tiles / raw mask; averaging: row-major uint8 / float32 map
 };
 static_assert(sizeof(ViewParams) == 96, "ViewParams layout");
+
+// ViewParams::kind of a carving view whose uint8 mask is read in place (two-tier masks: only the first views of a launch,
+// the ones every voxel meets, are bit-packed; the few voxels that survive them read the later masks raw):
+//   foreground = ((byte == ((kind >> 8) & 0xff)) ? 1 : 0) ^ ((kind >> 1) & 1)
+// which covers the three readings of nonzero_px<uint8_t>: plain (!= 0), BP_FLAG_INVERT (!= 255), BP_FLAG_BOOL_INVERT (== 0).
+constexpr uint32_t kViewRaw = 1u, kViewRawFlip = 2u;
+inline uint32_t raw_view_kind(uint32_t bp_flags) {  // bp_flags: BP_FLAG_INVERT = 1, BP_FLAG_BOOL_INVERT = 2
+    if (bp_flags & 2u) return kViewRaw | (0u << 8);                  // == 0
+    if (bp_flags & 1u) return kViewRaw | kViewRawFlip | (255u << 8); // != 255
+    return kViewRaw | kViewRawFlip | (0u << 8);                      // != 0
+}
 
 struct Batch {
     int n;
@@ -49,6 +60,41 @@ struct GridInfo {
     int sb_i, sb_j, sb_k;  // super-block extent in planes / CTA tiles
     int lg_i, lg_j, lg_k;
     int nsb_j, nsb_k;      // super-blocks along j and k
+};
+
+// ------------------------------------------------------------------------------------------
+// block cull of the carve path (cull_blocks_kernel / carve_items_kernel)
+// ------------------------------------------------------------------------------------------
+// A cull block is kBlkI planes x kBlkJ rows x kBlkK voxels = 16 warp patches of 4 (j) x 32 (k) voxels in one plane.
+constexpr int kBlkI = 8, kBlkJ = 8, kBlkK = 32;
+constexpr int kItemsPerBlock = kBlkI * (kBlkJ / 4) * (kBlkK / 32);
+constexpr int kItemsPerGrab = 4;   // warp patches a warp takes from the work list per atomic
+constexpr int kCullViews = 32;     // views (in visiting order) the block cull may use
+
+struct CullView {  // 96 bytes: what the block cull needs of one view
+    float cam[16];         // fx fy cx cy | rot[9] | tvec[3]
+    const uint32_t *sat;   // (tiles_y + 1) x (tpr + 1) summed-area table of "tile has a foreground bit"
+    int32_t tpr1;          // tpr + 1 (row pitch of sat)
+    int32_t W, H;
+    int32_t pad[3];
+};
+static_assert(sizeof(CullView) == 96, "CullView layout");
+
+struct SatJob {  // 32 bytes: build the summed-area table of one view's bit tiles
+    const uint32_t *tiles;
+    uint32_t *sat;
+    uint8_t *any;          // tiles_y x tpr scratch
+    int32_t tpr, tiles_y;
+};
+struct SatJobs {
+    int n;
+    int pad[3];
+    SatJob j[kCullViews];
+};
+
+struct CullGrid {
+    int nbi, nbj, nbk;       // cull blocks along i (local planes), j, k
+    uint32_t n_blocks;
 };
 
 // Batched fast path of the mask ingest: one PackJob per view of a chunk (see pack_bits_u8x16_kernel).

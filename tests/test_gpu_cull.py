@@ -1,0 +1,240 @@
+"""GPU parity tests of the round-2 carve path: the block cull (summed-area tables of the first views, whole blocks
+written off as carved, persistent dead flags, work list drained by persistent warps) and the two-tier masks (bit tiles
+for the first views of a launch, the caller's raw uint8 masks read in place for the rest).  Everything goes through
+the C ABI and is compared bit for bit with the CPU oracle and with the same library run with the cull switched off
+(``BP_CARVE_CULL=0``: the round-1 kernel that sweeps every patch).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import split_cam
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def BP():
+    from plant3dvision_b200.cl import Backprojection
+    return Backprojection
+
+
+@pytest.fixture(scope="module")
+def Oracle():
+    from oracle.backprojection_oracle import BackprojectionOracle
+    return BackprojectionOracle
+
+
+class env:
+    """Temporarily set environment switches the library reads at every call."""
+
+    def __init__(self, **kv):
+        self.kv = {k: str(v) for k, v in kv.items()}
+
+    def __enter__(self):
+        self.old = {k: os.environ.get(k) for k in self.kv}
+        os.environ.update(self.kv)
+
+    def __exit__(self, *exc):
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def synth_scene(name, scale, n_views=None):
+    from plant3dvision_b200 import synth
+    w = synth.workload(name, scale)
+    masks = synth.render_masks(w["cams"], w["capsules"], w["H"], w["W"]).numpy()
+    views = [(*split_cam(w["cams"][v]), masks[v]) for v in range(len(w["cams"]))]
+    return w, (views if n_views is None else views[:n_views])
+
+
+def oracle_volume(Oracle, w, views, default_value=0, shape=None):
+    ora = Oracle(shape or w["shape"], w["origin"], w["voxel_size"], type="carving", default_value=default_value)
+    for v in views:
+        ora.process_view(*v)
+    return ora.get_values()
+
+
+@pytest.mark.parametrize("name,scale", [("C5", 0.125), ("C2", 0.3), ("C4", 0.2)])
+def test_cull_equals_no_cull_equals_oracle(BP, Oracle, name, scale):
+    w, views = synth_scene(name, scale)
+    want = oracle_volume(Oracle, w, views)
+    got = {}
+    for cull in (1, 0):
+        with env(BP_CARVE_CULL=cull):
+            bp = BP(w["shape"], w["origin"], w["voxel_size"])
+            bp.process_views(views)
+            got[cull] = bp.get_values().copy()
+            _, blocks, dead = bp.work_stats()
+            bp.close()
+        if cull:
+            assert blocks > 0 and dead > 0.1 * blocks, f"the cull wrote off only {dead} of {blocks} blocks"
+        else:
+            assert dead == 0
+    assert np.array_equal(got[1], want), f"{(got[1] != want).sum()} voxels differ from the oracle with the cull on"
+    assert np.array_equal(got[0], want), f"{(got[0] != want).sum()} voxels differ from the oracle with the cull off"
+
+
+@pytest.mark.parametrize("shape", [[9, 9, 33], [8, 8, 32], [17, 7, 95], [1, 1, 1], [3, 70, 31], [40, 12, 200]])
+def test_cull_block_edges(BP, Oracle, shape):
+    """Grids that are not whole blocks (8 x 8 x 32 voxels) along any axis, and smaller than one block."""
+    w, views = synth_scene("C2", 0.2, n_views=20)
+    vs = 150.0 / max(shape)
+    ww = dict(w, voxel_size=vs)
+    want = oracle_volume(Oracle, ww, views, shape=shape)
+    bp = BP(shape, w["origin"], vs)
+    bp.process_views(views)
+    got = bp.get_values().copy()
+    bp.close()
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("p_fg", [1e-4, 3e-3])
+def test_isolated_foreground_pixels(BP, Oracle, p_fg):
+    """Masks that are background except for isolated single pixels: almost every tile is empty, so the cull fires
+    everywhere it may, and a block must survive exactly when one of its voxels lands on one of the lone pixels -
+    including pixels in the first / last row and column of a 32 x 32 tile."""
+    from plant3dvision_b200 import synth
+    w = synth.workload("C2", 0.25)
+    rng = np.random.default_rng(11)
+    views = []
+    for v in range(0, len(w["cams"]), 3):
+        m = np.where(rng.random((w["H"], w["W"])) < p_fg, 255, 0).astype(np.uint8)
+        m[31::32, 31::64] = 255   # tile corners
+        m[32::64, 0::32] = 255
+        views.append((*split_cam(w["cams"][v]), m))
+    want = oracle_volume(Oracle, w, views)
+    bp = BP(w["shape"], w["origin"], w["voxel_size"])
+    bp.process_views(views)
+    got = bp.get_values().copy()
+    bp.close()
+    assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ"
+    assert (want != -1).any()
+
+
+def test_dead_blocks_persist_over_launches_and_clear_resets_them(BP, Oracle):
+    """Host masks in several staging chunks (one carve launch per chunk) and the per-view streaming API: blocks written
+    off by an earlier launch are skipped by the later ones; ``clear()`` brings every block back."""
+    w, views = synth_scene("C5", 0.1, n_views=60)
+    want = oracle_volume(Oracle, w, views)
+    one_mask = views[0][3].nbytes
+    with env(BP_STAGE_BYTES=3 * one_mask):
+        bp = BP(w["shape"], w["origin"], w["voxel_size"])
+        bp.process_views(views)
+        np.testing.assert_array_equal(bp.get_values(), want)
+        _, blocks, dead = bp.work_stats()
+        assert dead > 0
+        # a different scene after clear(): nothing of the first one may linger
+        bp.clear()
+        assert bp.work_stats()[2] == 0
+        inv = [(i, r, t, np.invert(m)) for (i, r, t, m) in views[:12]]
+        bp.process_views(inv)
+        np.testing.assert_array_equal(bp.get_values(), oracle_volume(Oracle, w, inv))
+        bp.close()
+    # streaming: one launch per view
+    bp = BP(w["shape"], w["origin"], w["voxel_size"])
+    for v in views[:25]:
+        bp.process_view(*v)
+    np.testing.assert_array_equal(bp.get_values(), oracle_volume(Oracle, w, views[:25]))
+    assert bp.work_stats()[2] > 0
+    bp.close()
+
+
+@pytest.mark.parametrize("invert", [False, True])
+@pytest.mark.parametrize("head", [0, 1, 5, 40])
+def test_two_tier_masks_device_resident(BP, Oracle, head, invert):
+    """Device-resident uint8 masks: the first ``BP_PACK_HEAD`` views are bit-packed, the rest are read raw
+    (ld.global.nc.u8 in the dense / medium / sparse phases), plain and inverted readings.  Odd image widths included
+    (raw reads need no alignment)."""
+    import torch
+    from plant3dvision_b200 import synth
+    w = synth.workload("C2", 0.25)
+    H, W = w["H"], w["W"] - 3
+    cams = w["cams"].copy()
+    masks = synth.render_masks(cams, w["capsules"], H, W).numpy()
+    if invert:
+        masks = np.invert(masks)
+    n = 45
+    views = [(*split_cam(cams[v]), np.invert(masks[v]) if invert else masks[v]) for v in range(n)]
+    want = oracle_volume(Oracle, w, views)
+    md = torch.from_numpy(masks[:n].copy()).cuda()
+    ptrs = [md[v].data_ptr() for v in range(n)]
+    hw = np.tile(np.array([[H, W]], dtype=np.int32), (n, 1))
+    for cull in (1, 0):
+        with env(BP_PACK_HEAD=head, BP_CARVE_CULL=cull):
+            bp = BP(w["shape"], w["origin"], w["voxel_size"])
+            bp.process_device_views(cams[:n].astype(np.float32), ptrs, hw, invert=invert)
+            got = bp.get_values().copy()
+            bp.close()
+        assert np.array_equal(got, want), f"head {head} cull {cull}: {(got != want).sum()} voxels differ"
+
+
+def test_two_tier_speckle_walks_every_phase_on_raw_masks(BP, Oracle):
+    """Salt-and-pepper masks (see test_gpu_parity) read RAW from the second view on: the live count of every warp patch
+    decays through dense, medium and sparse (multi-view) phases on ld.global.nc.u8 reads."""
+    import torch
+    from plant3dvision_b200 import synth
+    w = synth.workload("C2", 0.2)
+    rng = np.random.default_rng(5)
+    n = len(w["cams"])
+    masks = np.where(rng.random((n, w["H"], w["W"])) < 0.04, 0, 255).astype(np.uint8)
+    views = [(*split_cam(w["cams"][v]), masks[v]) for v in range(n)]
+    want = oracle_volume(Oracle, w, views)
+    md = torch.from_numpy(masks).cuda()
+    hw = np.tile(np.array([[w["H"], w["W"]]], dtype=np.int32), (n, 1))
+    with env(BP_PACK_HEAD=1):
+        bp = BP(w["shape"], w["origin"], w["voxel_size"])
+        bp.process_device_views(w["cams"].astype(np.float32), [md[v].data_ptr() for v in range(n)], hw)
+        got = bp.get_values().copy()
+        bp.close()
+    assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ"
+
+
+def test_cull_on_striped_and_slab_handles(BP, Oracle):
+    """Plane-sharded handles: a cull block of 8 LOCAL planes spans non-contiguous global planes under stripes narrower
+    than a block; the bounds must still contain every voxel."""
+    w, views = synth_scene("C5", 0.1, n_views=40)
+    want = oracle_volume(Oracle, w, views)
+    nx = w["shape"][0]
+    for lg, world in ((0, 3), (1, 2), (3, 4)):
+        got = np.full_like(want, 77)
+        for rank in range(world):
+            s = BP(w["shape"], w["origin"], w["voxel_size"], stripes=(lg, world, rank))
+            s.process_views(views)
+            if len(s.planes):
+                got[s.planes] = s.get_values()
+            s.close()
+        np.testing.assert_array_equal(got, want, err_msg=f"stripes lg {lg} world {world}")
+    s = BP(w["shape"], w["origin"], w["voxel_size"], i_range=(nx // 3, nx - 5))
+    s.process_views(views)
+    np.testing.assert_array_equal(s.get_values(), want[nx // 3: nx - 5])
+    s.close()
+
+
+def test_default_values_with_cull(BP, Oracle):
+    w, views = synth_scene("C5", 0.08, n_views=30)
+    for d in (0, 5, -1, -3):
+        bp = BP(w["shape"], w["origin"], w["voxel_size"], default_value=d)
+        bp.process_views(views)
+        np.testing.assert_array_equal(bp.get_values(), oracle_volume(Oracle, w, views, default_value=d), err_msg=str(d))
+        bp.close()
+
+
+def test_counted_work_drops_with_the_cull(BP, monkeypatch):
+    """BP_COUNT_WORK=1 (counting variant of the kernels): the cull must cut the projections evaluated."""
+    w, views = synth_scene("C5", 0.125)
+    monkeypatch.setenv("BP_COUNT_WORK", "1")
+    work = {}
+    for cull in (0, 1):
+        with env(BP_CARVE_CULL=cull):
+            bp = BP(w["shape"], w["origin"], w["voxel_size"])
+            bp.process_views(views)
+            bp.sync()
+            work[cull] = bp.work_stats()[0]
+            bp.close()
+    nominal = int(np.prod(w["shape"])) * len(views)
+    assert 0 < work[1] < work[0] <= nominal * 1.01  # (padding lanes may count a little)
