@@ -113,10 +113,18 @@ class Backprojection(object):
     i_range : (int, int), optional (keyword only)
         Hold only planes ``[i0, i1)`` of axis 0 (slab sharding). ``get_values`` then returns
         ``[i1 - i0, ny, nz]``.
+    speculative_readback : bool, optional (keyword only)
+        Carving: let the library start copying the volume into ``values_h`` while host masks are still being uploaded
+        (PCIe is full duplex; carved voxels are final), so that ``get_values`` only sends the rows that changed since.
+        Same values as without it.  The one observable difference: ``values_h`` - the buffer a PREVIOUS ``get_values``
+        returned a view of, as in the reference (cl.py:229-232) - may be rewritten during ``process_views`` /
+        ``process_fileset`` instead of only inside the next ``get_values``; copy a result you want to keep across
+        further views (the reference's own callers do, cl.py:249-254).  Default: on (``BP_SPEC_READBACK=0`` or
+        ``False`` here switches it off).
     """
 
     def __init__(self, shape, origin, voxel_size, type="carving", default_value=0, labels=None, log=False,
-                 *, device=None, i_range=None, stripes=None):
+                 *, device=None, i_range=None, stripes=None, speculative_readback=None):
         self.shape = shape
         self.origin = origin
         self.voxel_size = voxel_size
@@ -132,6 +140,11 @@ class Backprojection(object):
         else:
             raise ValueError(f"Unknown kernel type {type}, valid values are 'averaging' or 'carving'!")
         self.kernel = type  # the reference stores the OpenCL kernel object here
+        # Speculative read-back of the carve volume (see _register_readback_target): on unless switched off here or
+        # with BP_SPEC_READBACK=0
+        if speculative_readback is None:
+            speculative_readback = os.environ.get("BP_SPEC_READBACK", "1") not in ("", "0")
+        self.speculative_readback = bool(speculative_readback)
         if device is None:
             import os
             device = int(os.environ.get("LOCAL_RANK", "0"))
@@ -296,10 +309,9 @@ class Backprojection(object):
             self._process_batch(views[s:s + MAX_VIEWS_PER_CALL], invert)
 
     def _register_readback_target(self):
-        """``BP_SPEC_READBACK=1`` (experimental): tell the library where ``get_values`` will want the carve volume, so
-        that it can send an early copy while masks are still being uploaded (bp_set_readback_target)."""
-        if (self._spec_registered or self._mode != _cabi.MODE_CARVING
-                or os.environ.get("BP_SPEC_READBACK", "0") in ("", "0")):
+        """Tell the library where ``get_values`` will want the carve volume, so that it can send an early copy while
+        masks are still being uploaded (bp_set_readback_target; see ``speculative_readback``)."""
+        if self._spec_registered or self._mode != _cabi.MODE_CARVING or not self.speculative_readback:
             return
         buf = self.values_h
         if buf.size:
@@ -387,7 +399,7 @@ class Backprojection(object):
         """Upload + bit-pack ``masks`` (2-D uint8 / bool arrays, or with ``device_masks`` device addresses of
         uint8 arrays whose sizes are ``hw``) to ``dst_ptr + q * view_stride`` in device memory.  Carving only.
         ``cams`` (float32 ``[n, 16]``, optional): lets the library trim each view to the rectangle the whole grid
-        projects into when ``BP_VIEW_RECT=1`` (bp_pack_views_cams)."""
+        projects into (bp_pack_views_cams; ``BP_VIEW_RECT=0`` switches the trimming off)."""
         n = len(masks)
         if n == 0:
             return

@@ -30,8 +30,10 @@ void pack_bits(cudaStream_t st, int dtype, const void *src, uint32_t *out, int H
 // mask ingest, batched fast path (uint8, 16-byte aligned rows): every view of a chunk in one launch
 void pack_u8x16(dim3 grd, cudaStream_t st, uint32_t *pool, const PackJobs &jobs, uint32_t flags);
 // read-back helpers
-void expand_state(cudaStream_t st, const int8_t *state, int32_t *out, size_t n, int nz, int nzp, int v_carved, int v_seen,
-                  int v_unseen);
+void expand_state(cudaStream_t st, const int8_t *state, int32_t *out, size_t n_rows, int nz, int nzp, int v_carved,
+                  int v_seen, int v_unseen);
+// bit s of *present (zeroed by the caller) is set when carve state s occurs among the unpadded voxels
+void state_presence(cudaStream_t st, const int8_t *state, size_t n_rows, int nz, int nzp, uint32_t *present);
 void patch_rows(cudaStream_t st, const int8_t *state, const int8_t *snap, int32_t *host_out, size_t n_rows, int nz, int nzp,
                 int v_carved, int v_seen, int v_unseen, unsigned long long *count);
 void unpad_f32(cudaStream_t st, const float *in, float *out, size_t n, int nz, int nzp);

@@ -13,11 +13,13 @@
 namespace {
 using namespace bph;
 
-// BP_VIEW_RECT=1: copy (host masks) and pack only the rectangle of every view that the handle's planes project
-// into (view_rect).  Read at every call so that a test can switch it.  Off by default until measured.
+// View rectangles: copy (host masks) and pack only the rectangle of every view that the handle's planes project into
+// (bp_box_rect: pixels outside it are never sampled by any voxel of the handle).  On by default since round 2 (C5: the
+// 1024^3 box fills 61.5 % of a 6000 x 4000 view; e2e 185 -> 146 ms, profiles/r02_bench_view_rect.json); BP_VIEW_RECT=0
+// switches it off.  Read at every call so that a test can switch it.
 bool view_rect_enabled() {
     const char *e = std::getenv("BP_VIEW_RECT");
-    return e && std::atoi(e) != 0;
+    return !e || std::atoi(e) != 0;
 }
 
 // BP_CARVE_CULL=0 switches the block cull off: every launch then sweeps every patch of the grid with carve_kernel

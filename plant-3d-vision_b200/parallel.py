@@ -137,6 +137,7 @@ class DistributedBackprojection(object):
             # contiguous slabs the carve kernel of the middle ranks runs 2x longer than the mean (measured at
             # G = 8, profiles/r01_bench_n8_v9.json); same exactness argument as slabs
             lg = int(engine_kwargs.pop("stripe_lg", 3))
+            self._stripe_lg = lg
             engine_kwargs["stripes"] = (lg, self.world, self.rank)
             self.planes = np.array([i for i in range(self.shape[0]) if (i >> lg) % self.world == self.rank])
             self.i_range = (int(self.planes[0]) if len(self.planes) else 0,
@@ -149,6 +150,9 @@ class DistributedBackprojection(object):
         self.local = engine(self.shape, origin, voxel_size, type=type, default_value=local_default, labels=labels,
                             log=log, **engine_kwargs)
         self._reduced = True  # nothing accumulated yet
+        # view-sharded averaging: after a SUM all-reduce EVERY rank holds the total; before more views are added the
+        # ranks != 0 must start again from 0, or the next reduce would count the total world-size times
+        self._holds_total = False
         if ingest not in ("auto", "sharded", "replicated"):
             raise ValueError(f"Unknown ingest {ingest!r}")
         # slab sharding needs every mask on every rank.  "sharded": a rank uploads (PCIe) and bit-packs only
@@ -219,9 +223,9 @@ class DistributedBackprojection(object):
                 cur.wait_event(done[ci & 1])      # NCCL / copies must not overwrite what a pass still reads
             if carving:
                 # (the engine's own stream is already ordered behind that pass)
-                # experimental (BP_VIEW_RECT=1): with the cameras the library uploads and packs only the rectangle of
-                # each view that the whole grid projects into
-                rect = os.environ.get("BP_VIEW_RECT", "0") not in ("", "0")
+                # with the cameras the library uploads and packs only the rectangle of each view that the whole grid
+                # projects into (BP_VIEW_RECT=0 switches that off)
+                rect = os.environ.get("BP_VIEW_RECT", "1") not in ("", "0")
                 self.local.pack_views([masks[v] for v in mine], buf[r].data_ptr(), stride, invert=invert,
                                       **({"cams": np.asarray(cams, dtype=np.float32).reshape(-1, 16)[mine]} if rect else {}))
                 ev = torch.cuda.Event()
@@ -247,10 +251,20 @@ class DistributedBackprojection(object):
             if ev is not None:
                 ev.synchronize()
 
+    def _before_more_views(self):
+        """The reference API allows process_view, get_values, process_view, get_values (cl.py:190-232).  Under view
+        sharding ``get_values`` leaves the all-reduced volume on every rank: for averaging (SUM) only rank 0 may keep it
+        as the base of further accumulation, the others restart from 0 (their seed).  MIN (carving) is idempotent."""
+        if self._holds_total:
+            if self.rank != 0:
+                self.local.clear()
+            self._holds_total = False
+
     def process_device_views(self, cams, mask_ptrs, hw, invert=False):
         """Masks resident in HBM on every rank (device addresses of uint8 / float32 arrays): nothing to exchange,
         every rank ingests from its own copy (packing 1/G each and all-gathering the tiles was measured slower
         than packing everything locally at 3.7 TB/s: profiles/r01_bench_n2_*.json)."""
+        self._before_more_views()
         if self.sharding == "views":
             mine = self.my_views(len(mask_ptrs))
             cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(-1, 16)[mine]
@@ -264,6 +278,7 @@ class DistributedBackprojection(object):
         """``views``: the FULL sequence of ``(intrinsics, rot, tvec, mask)``, identical on every rank
         (a rank only touches the masks of the views it owns)."""
         views = list(views)
+        self._before_more_views()
         if views and self._can_shard_ingest([np.shape(v[3]) for v in views], [np.asarray(v[3]).dtype for v in views]):
             n = len(views)
             cams = np.empty((n, 16), dtype=np.float32)
@@ -283,6 +298,7 @@ class DistributedBackprojection(object):
 
     def process_view(self, intrinsics, rot, tvec, mask):
         """One view on every rank's grid part (slabs) / on the rank whose turn it is (views)."""
+        self._before_more_views()
         if self.sharding == "views":
             turn = getattr(self, "_turn", 0)
             self._turn = turn + 1
@@ -307,6 +323,7 @@ class DistributedBackprojection(object):
                 continue
             usable.append((fi, cam))
         from .cl import _read_image
+        self._before_more_views()
         mine = []
         for v in self.my_views(len(usable)):
             fi, cam = usable[v]
@@ -368,21 +385,56 @@ class DistributedBackprojection(object):
         dist.all_reduce(state, op=op, group=self.group)
         self.local.adopt_state(state)
         self._reduced = True
+        self._holds_total = self.type == "averaging"
+
+    def _planes_of(self, rank):
+        nx = self.shape[0]
+        if self.sharding == "slabs":
+            a, b = slab_range(nx, rank, self.world)
+            return np.arange(a, b)
+        lg = self._stripe_lg
+        return np.array([i for i in range(nx) if (i >> lg) % self.world == rank], dtype=np.int64)
+
+    def _gather_planes(self, vol):
+        """Plane sharding: every rank's ``[n_local, ny, nz]`` part -> the full ``[nx, ny, nz]`` volume on every rank.
+        ONE tensor all-gather (the parts padded to the largest plane count).  With NCCL and a CUDA engine the raw
+        device state travels over NVLink - int8 for carving, a quarter of the reference's int32 - and is decoded on
+        the host after a single D2H; on CPU ranks (gloo) the numpy parts are gathered."""
+        import torch
+        dist = _dist()
+        counts = [len(self._planes_of(r)) for r in range(self.world)]
+        n_max = max(counts)
+        nccl = str(dist.get_backend(self.group)) == "nccl"
+        if nccl and hasattr(self.local, "device_state"):
+            self.local.sync()
+            st = self.local.state_tensor()  # [n_local, ny, nz_pitch] int8 / float32, aliases the engine's state
+            send = torch.zeros((n_max,) + tuple(st.shape[1:]), dtype=st.dtype, device=st.device)
+            send[:st.shape[0]].copy_(st)
+            recv = torch.empty((self.world,) + tuple(send.shape), dtype=st.dtype, device=st.device)
+            dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=self.group)
+            parts = recv.cpu().numpy()[..., :self.shape[2]]
+            if self.type == "carving":
+                parts = decode_carve_state(parts, self.default_value)
+        else:
+            send = torch.zeros((n_max,) + tuple(vol.shape[1:]), dtype=torch.from_numpy(np.empty(0, vol.dtype)).dtype)
+            send[:vol.shape[0]] = torch.from_numpy(np.ascontiguousarray(vol))
+            recv = [torch.empty_like(send) for _ in range(self.world)]
+            dist.all_gather(recv, send, group=self.group)
+            parts = [t.numpy() for t in recv]
+        out = np.empty((self.shape[0], *vol.shape[1:]), dtype=vol.dtype)
+        for r in range(self.world):
+            out[self._planes_of(r)] = parts[r][:counts[r]]
+        return out
 
     def get_values(self, gather=True):
         """The volume (cl.py:229-232).  Views: the full grid on every rank, after ``reduce()``.
         Slabs: this rank's planes, or with ``gather`` the full grid all-gathered on every rank."""
         self.reduce()
-        vol = self.local.get_values()
         if self.sharding == "views" or self.world == 1 or not gather:
-            return vol
-        dist = _dist()
-        parts = [None] * self.world
-        dist.all_gather_object(parts, (self.planes, np.ascontiguousarray(vol)), group=self.group)
-        out = np.empty((self.shape[0], *vol.shape[1:]), dtype=vol.dtype)
-        for planes, part in parts:
-            out[planes] = part
-        return out
+            return self.local.get_values()
+        if str(_dist().get_backend(self.group)) == "nccl" and hasattr(self.local, "device_state"):
+            return self._gather_planes(np.empty((0, self.shape[1], self.shape[2]), dtype=self.dtype))
+        return self._gather_planes(self.local.get_values())
 
     get_volume = get_values
 
@@ -390,6 +442,7 @@ class DistributedBackprojection(object):
         self.local.clear()
         self._turn = 0
         self._reduced = True
+        self._holds_total = False
 
     def close(self):
         self.local.close()

@@ -136,6 +136,30 @@ def worker(rank, world, port, kind, sharding, default_value, out_dir, backend="g
         dist.destroy_process_group()
 
 
+def worker_incremental(rank, world, port, kind, sharding, out_dir):
+    """The reference API allows process_view(s), get_values, process_view(s), get_values (cl.py:190-232): the second
+    result must be the sequential one over ALL views, not the first total counted once per rank."""
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from plant3dvision_b200.parallel import DistributedBackprojection
+        shape, origin, vs, views = scene()
+        bp = DistributedBackprojection(shape, origin, vs, type=kind, default_value=0.25 if kind == "averaging" else 0,
+                                       log=False, sharding=sharding, engine=OracleEngine)
+        bp.process_views(views[:3])
+        first = np.array(bp.get_values(gather=True))
+        bp.process_views(views[3:5])
+        second = np.array(bp.get_values(gather=True))
+        for v in views[5:]:
+            bp.process_view(*v)
+        third = np.array(bp.get_values(gather=True))
+        np.savez(os.path.join(out_dir, f"inc{rank}.npz"), first=first, second=second, third=third)
+    finally:
+        dist.destroy_process_group()
+
+
 def worker_voxels_task(rank, world, port, scan_dir, sharding, out_dir):
     """The Voxels task mirror over a distributed engine: every rank computes, rank 0 writes."""
     import torch.distributed as dist

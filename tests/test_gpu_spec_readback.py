@@ -1,10 +1,8 @@
-"""EXPERIMENTAL (written without GPU time left in round 1, so not yet part of the default GPU suite): speculative
-read-back of the carve volume (bp_set_readback_target, BP_SPEC_READBACK=1).  With host masks arriving in several
-staging chunks the library sends an early copy of the volume to the pinned host buffer while the remaining masks
-are still being uploaded, and get_values() only writes the rows that changed since.  The values must be exactly
-what get_values() returns without it.
-
-Run with  BP_EXPERIMENTAL=1 python -m pytest tests/test_gpu_spec_readback.py -m gpu -q
+"""Speculative read-back of the carve volume (bp_set_readback_target; default since round 2, ``BP_SPEC_READBACK=0`` or
+``Backprojection(..., speculative_readback=False)`` switches it off).  With host masks arriving in several staging
+chunks the library sends an early copy of the volume to the pinned host buffer while the remaining masks are still
+being uploaded, and get_values() only writes the rows that changed since.  The values must be exactly what
+get_values() returns without it.  First run on a B200 in round 2 (profiles/r02_pytest_spec_readback.log).
 """
 import os
 
@@ -13,8 +11,7 @@ import pytest
 
 from conftest import split_cam
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("BP_EXPERIMENTAL") != "1", reason="experimental: set BP_EXPERIMENTAL=1")]
+pytestmark = pytest.mark.gpu
 
 
 def _scene(scale=0.064, step=4):

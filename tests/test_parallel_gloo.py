@@ -65,6 +65,30 @@ def test_two_ranks_equal_sequential(tmp_path, kind, sharding, default_value):
             assert np.array_equal(z["part"], want[i0:i1])
 
 
+@pytest.mark.parametrize("kind,sharding", [("averaging", "views"), ("carving", "views"), ("averaging", "stripes")])
+def test_more_views_after_get_values(tmp_path, kind, sharding):
+    """under view sharding a SUM all-reduce leaves the total on every rank; views processed after a
+    get_values() must be added to it ONCE, not to world-size copies of it."""
+    from _gloo_worker import worker_incremental
+    world = 2
+    spawn(worker_incremental, world, kind, sharding, str(tmp_path))
+    shape, origin, vs, views = scene()
+    o = BackprojectionOracle(shape, origin, vs, type=kind, default_value=0.25 if kind == "averaging" else 0)
+    want = []
+    for upto in (3, 5, len(views)):
+        while len(want) < 3 and getattr(o, "_n", 0) < upto:
+            o.process_view(*views[getattr(o, "_n", 0)])
+            o._n = getattr(o, "_n", 0) + 1
+        want.append(o.get_values().copy())
+    for rank in range(world):
+        z = np.load(tmp_path / f"inc{rank}.npz")
+        for got, w in zip((z["first"], z["second"], z["third"]), want):
+            if kind == "carving" or sharding != "views":
+                assert np.array_equal(got, w)
+            else:
+                np.testing.assert_allclose(got, w, rtol=1e-5, atol=1e-6)
+
+
 def test_slab_range_and_view_partition_cover_everything():
     for nx in (1, 7, 128, 1024, 1025):
         for world in (1, 2, 3, 8):
