@@ -51,9 +51,10 @@ def main():
     for c in CHANNELS:
         maps[c] = np.stack(maps[c])
         assert maps[c].dtype == np.uint8 and maps[c].shape == (18, 896, 896)
-    np.savez_compressed(f"{HERE}/virtual_plant_inputs.npz", cams=cams,
-                        bbox=np.array([bbox["x"], bbox["y"], bbox["z"]], dtype=np.float64),
-                        **{f"map_{c}": maps[c] for c in CHANNELS})
+    if len(sys.argv) <= 1:  # (adding one golden entry leaves the committed inputs file alone)
+        np.savez_compressed(f"{HERE}/virtual_plant_inputs.npz", cams=cams,
+                            bbox=np.array([bbox["x"], bbox["y"], bbox["z"]], dtype=np.float64),
+                            **{f"map_{c}": maps[c] for c in CHANNELS})
 
     def run(backend, kind, vs, label="background", log=False, invert=None):
         shape, origin = shape_origin(bbox, vs)
@@ -68,8 +69,16 @@ def main():
 
     out = {}
     meta = {}
-    # carving (geom_pipe_virtual.toml: background channel, invert, camera metadata "camera")
-    for vs in (0.6, 0.3, 0.1):
+    only = sys.argv[1] if len(sys.argv) > 1 else None  # e.g. `make_golden.py carve_vs0.06`: add one entry, keep the rest
+    if only:
+        with np.load(f"{HERE}/virtual_plant_golden.npz") as z:
+            meta = json.loads(str(z["meta"]))
+            out = {k: z[k] for k in z.files if k != "meta"}
+    # carving (geom_pipe_virtual.toml: background channel, invert, camera metadata "camera"; voxel_size 0.06 is the
+    # value configs/geom_pipe_virtual.toml:6 sets - 386 x 397 x 1998 voxels - and 0.1 the CI variant's)
+    for vs in (0.6, 0.3, 0.1, 0.06):
+        if only and only != f"carve_vs{vs}":
+            continue
         vol = run("ref_off", "carving", vs)
         fma = run("ref_fma", "carving", vs)
         key = f"carve_vs{vs}"
@@ -82,6 +91,8 @@ def main():
     # averaging, 6 labels (ml_pipe_virtual.toml: voxel_size 0.3, log False; task default log True)
     for vs, log in ((0.6, False), (0.6, True), (0.3, False), (0.3, True)):
         for label in CHANNELS:
+            if only and only != f"avg_vs{vs}_log{int(log)}_{label}":
+                continue
             vol = run("ref_off", "averaging", vs, label=label, log=log, invert=False)
             fma = run("ref_fma", "averaging", vs, label=label, log=log, invert=False)
             key = f"avg_vs{vs}_log{int(log)}_{label}"

@@ -43,7 +43,7 @@ def sha(a):
 # ---------------------------------------------------------------------------------------------
 # golden vectors: reference kernel source on the reference's virtual_plant fixture
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("vs", [0.6, 0.3, 0.1])
+@pytest.mark.parametrize("vs", [0.6, 0.3, 0.1, 0.06])  # 0.06 = configs/geom_pipe_virtual.toml:6 (BASELINE.json configs[0])
 @pytest.mark.parametrize("fused", [True, False])
 def test_golden_carving(BP, vp_inputs, vp_golden, vs, fused):
     shape, origin = vp_shape_origin(vp_inputs["bbox"], vs)
