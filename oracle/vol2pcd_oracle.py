@@ -8,6 +8,12 @@ The two third-party calls are the reference's own dependencies, imported here di
 the reference's requirements; this image has scipy 1.18).  ``multiclass_select`` restates
 /root/reference/plant3dvision/tasks/proc3d.py:80-115 (argmax + contrast / score gates).
 
+PARITY PINNING: pinned to the reference's own text - tests/golden/make_golden_f.py cuts `vol2pcd`, `index2point`,
+`backproject_points` and the scoring loop of `SegmentedPointCloud.run` out of the reference's source files and executes
+them as written; tests/test_f_rows_golden.py checks this module against the committed outputs
+(tests/golden/f_rows_golden.npz): bit-identical for the per-point loop form and the scoring, <= 1e-12 for the
+vectorised form (np.linalg.norm vs x*x + y*y + z*z).
+
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this module.
 """
 import numpy as np
