@@ -408,7 +408,7 @@ def run_reference(args):
     cores = os.cpu_count() or 1
     os.environ.setdefault("OMP_NUM_THREADS", str(cores))
     nx = int(w["shape"][0])
-    n_pl = args.cpu_planes or max(2, auto_planes(w, mode) // 2)
+    n_pl = args.cpu_planes or max(2, auto_planes(w, mode) // 4)
     planes = sample_planes(range(nx), n_pl)
     per_sample_vv = float(len(planes)) * w["shape"][1] * w["shape"][2] * len(w["cams"])
 

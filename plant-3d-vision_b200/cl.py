@@ -146,7 +146,6 @@ class Backprojection(object):
             speculative_readback = os.environ.get("BP_SPEC_READBACK", "1") not in ("", "0")
         self.speculative_readback = bool(speculative_readback)
         if device is None:
-            import os
             device = int(os.environ.get("LOCAL_RANK", "0"))
         self.device = int(device)
         nx = int(self.shape[0])
