@@ -109,8 +109,9 @@ class Voxels:
 
     Parameters are those of the reference task; ``scan`` is an ``fsdb_lite.Scan`` (or a path)."""
 
-    def __init__(self, scan, masks_fileset=None, **params):
+    def __init__(self, scan, masks_fileset=None, colmap_fileset=None, **params):
         self.scan = scan if hasattr(scan, "get_fileset") else fsdb_lite.Scan(scan)
+        self._colmap_fileset = colmap_fileset
         unknown = set(params) - set(DEFAULTS)
         if unknown:
             raise TypeError(f"Unknown Voxels parameters: {sorted(unknown)}")
@@ -129,7 +130,7 @@ class Voxels:
         if bbox is None:
             bbox = self.scan.get_metadata("bounding_box")
         if bbox is None and self.upstream_colmap == "Colmap":
-            colmap_fs = _find_fileset(self.scan, "Colmap")
+            colmap_fs = self._colmap_fileset or _find_fileset(self.scan, "Colmap")
             if colmap_fs is not None:
                 bbox = colmap_fs.get_metadata("bounding_box")
         if bbox is None:
@@ -248,4 +249,78 @@ def run_voxels(scan_dir, config=None, backprojection_class=None, bp_kwargs=None,
     else:
         params = parse_params(config, strict=False)
     params.update(overrides)
-    return Voxels(scan_dir, **params).run(backprojection_class, **(bp_kwargs or {}))
+    return VoxelsRunner(scan_dir, **params).run(backprojection_class, **(bp_kwargs or {}))
+
+
+# ---------------------------------------------------------------------------------------------
+# luigi / romitask registration
+# ---------------------------------------------------------------------------------------------
+#: the plain, dependency-free runner under a name that never changes
+VoxelsRunner = Voxels
+
+
+def make_luigi_voxels():
+    """The ``Voxels`` luigi task of the reference (plant3dvision/tasks/cl.py:18-186: same task family, same
+    ``luigi.*Parameter`` attributes and defaults, same ``requires()``), running on this package's ``Backprojection``.
+    Needs luigi + romitask (+ plantdb for the writers); ``romitask/modules.py:43`` maps the name ``Voxels`` to a module
+    path - pointing it at ``plant3dvision_b200.tasks.cl`` is the whole integration."""
+    import luigi
+    from romitask import RomiTask
+
+    def _upstream(name, module):
+        try:
+            mod = __import__(module, fromlist=[name])
+            return luigi.TaskParameter(default=getattr(mod, name))
+        except ImportError:  # plant3dvision itself not installed: the task must then be given explicitly
+            return luigi.TaskParameter()
+
+    class Voxels(RomiTask):
+        upstream_task = None  # override default attribute from ``RomiTask``
+        upstream_mask = _upstream("Masks", "plant3dvision.tasks.proc2d")
+        upstream_colmap = _upstream("Colmap", "plant3dvision.tasks.colmap")
+
+        query = luigi.DictParameter(default={})
+        camera_metadata = luigi.Parameter(default='colmap_camera')
+        voxel_size = luigi.FloatParameter(default=1.0)
+        type = luigi.Parameter(default="carving")
+        log = luigi.BoolParameter(default=True)
+
+        invert = luigi.BoolParameter(default=False)
+        labels = luigi.ListParameter(default=[])
+        bounding_box = luigi.DictParameter(default=None)
+
+        def requires(self):
+            if self.upstream_colmap.get_task_family() == 'Colmap':
+                return {'masks': self.upstream_mask(), 'colmap': self.upstream_colmap()}
+            else:
+                return {'masks': self.upstream_mask()}
+
+        def run(self):
+            masks_fileset = self.input()['masks'].get()
+            uses_colmap = self.upstream_colmap.get_task_family() == 'Colmap'
+            colmap_fileset = self.input()['colmap'].get() if uses_colmap else None
+            runner = VoxelsRunner(
+                masks_fileset.scan, masks_fileset=masks_fileset, colmap_fileset=colmap_fileset,
+                upstream_colmap="Colmap" if uses_colmap else self.upstream_colmap.get_task_family(),
+                query=dict(self.query), camera_metadata=str(self.camera_metadata), voxel_size=float(self.voxel_size),
+                type=str(self.type), log=bool(self.log), invert=bool(self.invert), labels=list(self.labels),
+                bounding_box=None if self.bounding_box is None else {k: list(v) for k, v in dict(self.bounding_box).items()})
+            vol, labels, origin = runner.compute()
+            outfile = self.output_file()
+            from plantdb import io
+            if labels is not None:
+                io.write_npz(outfile, {label: vol[i, :] for i, label in enumerate(labels)})
+            else:
+                io.write_volume(outfile, vol)
+            outfile.set_metadata({'voxel_size': self.voxel_size, 'origin': [float(o) for o in origin]})
+
+    return Voxels
+
+
+try:  # registered only where the reference's task framework exists; everywhere else `Voxels` is the plain runner
+    import luigi as _luigi  # noqa: F401
+    import romitask as _romitask  # noqa: F401
+except ImportError:
+    pass
+else:
+    Voxels = make_luigi_voxels()

@@ -162,3 +162,84 @@ def test_segmented_point_cloud_task_host_logic(tmp_path, monkeypatch):
     out2 = tp.SegmentedPointCloud(str(scan_dir), use_colmap_poses=True, labels=["stem", "leaf"]).run()
     assert seen["calls"] == [] and set(out2.get_metadata("labels")) == {"stem"}  # all-zero scores: first label
     assert out2.id == "SegmentedPointCloud"
+
+
+def test_voxels_registers_as_a_luigi_task_when_the_framework_is_importable(tmp_path, monkeypatch):
+    """with luigi + romitask importable, ``plant3dvision_b200.tasks.cl.Voxels`` is a RomiTask with the
+    reference's parameters (tasks/cl.py:79-91) and ``requires()`` (:93-97); ``run()`` reads its inputs through the
+    task framework and writes through plantdb's io, like the reference (:99-186).  The framework is absent from this
+    image, so minimal stand-ins are put in ``sys.modules`` - what is exercised is this package's side of the glue."""
+    import sys
+    import types
+    import plant3dvision_b200.cl as bcl
+    from plant3dvision_b200 import fsdb_lite
+    from plant3dvision_b200.tasks import cl as tcl
+
+    class Param:
+        def __init__(self, default=None):
+            self.default = default
+
+    luigi = types.ModuleType("luigi")
+    for n in ("Parameter", "DictParameter", "FloatParameter", "BoolParameter", "ListParameter", "TaskParameter"):
+        setattr(luigi, n, type(n, (Param,), {}))
+
+    class RomiTask:
+        def __init__(self, **kw):
+            for k in dir(type(self)):
+                v = getattr(type(self), k)
+                if isinstance(v, Param):
+                    setattr(self, k, kw.get(k, v.default))
+
+    romitask = types.ModuleType("romitask")
+    romitask.RomiTask = RomiTask
+    written = {}
+    plantdb = types.ModuleType("plantdb")
+    plantdb.io = types.ModuleType("plantdb.io")
+    plantdb.io.write_npz = lambda f, d: written.update(npz=d)
+    plantdb.io.write_volume = lambda f, v: written.update(vol=v)
+    for name, mod in (("luigi", luigi), ("romitask", romitask), ("plantdb", plantdb), ("plantdb.io", plantdb.io)):
+        monkeypatch.setitem(sys.modules, name, mod)
+    monkeypatch.setattr(bcl, "Backprojection", OracleEngine)
+
+    Task = tcl.make_luigi_voxels()
+    assert Task.__name__ == "Voxels" and issubclass(Task, RomiTask) and Task.upstream_task is None
+    want = {"query": {}, "camera_metadata": "colmap_camera", "voxel_size": 1.0, "type": "carving", "log": True,
+            "invert": False, "labels": [], "bounding_box": None}
+    for k, v in want.items():
+        assert getattr(Task, k).default == v, k  # the reference's defaults
+
+    scan_dir = make_scan(tmp_path, n=3, channels=("background", "stem"))
+    images = fsdb_lite.Scan(str(scan_dir)).get_fileset("images")
+
+    class Target:
+        def __init__(self, fs):
+            self.fs = fs
+
+        def get(self):
+            return self.fs
+
+    class Upstream:
+        @staticmethod
+        def get_task_family():
+            return "ImagesFilesetExists"
+
+    class OutFile:
+        md = None
+
+        def set_metadata(self, md):
+            OutFile.md = md
+
+    t = Task(upstream_mask=Upstream, upstream_colmap=Upstream, type="averaging", log=False, camera_metadata="camera",
+             labels=["stem", "background"])
+    assert set(t.requires()) == {"masks"}  # no Colmap upstream -> only the masks
+    monkeypatch.setattr(Upstream, "__call__", lambda self: None, raising=False)
+    t.input = lambda: {"masks": Target(images)}
+    t.output_file = lambda: OutFile()
+    t.run()
+    eng = OracleEngine([9, 7, 5], [-4.0, -3.0, -2.0], 1.0, type="averaging", labels=["stem", "background"], log=False)
+    ref = eng.process_fileset(images.get_files(), "camera")
+    assert list(written["npz"]) == ["stem", "background"]
+    assert np.array_equal(written["npz"]["stem"], ref[0]) and np.array_equal(written["npz"]["background"], ref[1])
+    assert OutFile.md == {"voxel_size": 1.0, "origin": [-4.0, -3.0, -2.0]}
+    # without the framework (this image) the module-level name stays the plain runner
+    assert tcl.Voxels is tcl.VoxelsRunner
