@@ -601,10 +601,11 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
             files = mem_fileset(w, masks)
 
             def step_e2e():
+                bp.clear()  # (process_fileset clears BETWEEN labels, cl.py:249-252: a fresh grid is the caller's job)
                 if world > 1:
                     return bp.process_fileset(files, "camera", invert=w["invert"], gather=False)
                 return bp.process_fileset(files, "camera", invert=w["invert"])
-            api = "Backprojection.process_fileset(files, 'camera', invert=%s)" % w["invert"]
+            api = "clear(); Backprojection.process_fileset(files, 'camera', invert=%s)" % w["invert"]
         else:
             m0 = masks[None]
             views_host = [(cams[v, 0:4], cams[v, 4:13], cams[v, 13:16], m0[v]) for v in range(n_views)]

@@ -45,6 +45,7 @@ struct bp_handle {
     CullGrid cg{};
     uint8_t *blk_dead = nullptr;        // one byte per cull block, persistent until bp_clear
     uint2 *blk_live = nullptr;          // work list of one launch
+    uint2 *blk_cand = nullptr;          // survivors of the cull's first pass
     uint32_t *cull_counters = nullptr;  // {live blocks, next work item, blocks killed, -}
     CullView *cull_views_d = nullptr;   // kCullViews entries
     void *sat_pool = nullptr;           // summed-area tables (+ scratch) of one launch

@@ -70,6 +70,7 @@ constexpr int kBlkI = 8, kBlkJ = 8, kBlkK = 32;
 constexpr int kItemsPerBlock = kBlkI * (kBlkJ / 4) * (kBlkK / 32);
 constexpr int kItemsPerGrab = 4;   // warp patches a warp takes from the work list per atomic
 constexpr int kCullViews = 32;     // views (in visiting order) the block cull may use
+constexpr int kCullFirstViews = 3; // ... of which the first pass (every block) takes these; the rest see survivors only
 
 struct CullView {  // 96 bytes: what the block cull needs of one view
     float cam[16];         // fx fy cx cy | rot[9] | tvec[3]

