@@ -318,6 +318,15 @@ class Backprojection(object):
             self._keep.append(self._values)
         self._spec_registered = True
 
+    def spec_snapshot(self):
+        """Start the speculative read-back NOW: the carve volume as it stands begins its way to ``values_h`` while the
+        caller goes on feeding views (bp_spec_snapshot; used by the multi-GPU sharded ingest, whose masks reach the
+        library already packed, in chunks the library cannot foresee).  No-op unless ``speculative_readback``."""
+        if self._mode != _cabi.MODE_CARVING or not self.speculative_readback:
+            return
+        self._register_readback_target()
+        _cabi.check(_cabi.lib().bp_spec_snapshot(self._handle()))
+
     def spec_stats(self):
         """(rows written, rows compared) by the last speculative ``get_values`` (bp_spec_stats)."""
         a, b = ctypes.c_int64(), ctypes.c_int64()

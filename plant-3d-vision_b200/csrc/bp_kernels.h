@@ -16,11 +16,12 @@ void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewP
 // block cull of the carve path: summed-area tables of "tile has a foreground bit" for the views of `jobs`
 // (two launches), the cull itself (dead flags, zero fill of the blocks it kills, work list of the survivors;
 // counters = {live blocks, next work item, blocks killed, candidates after the first pass}, zeroed by the caller;
-// two launches: the first n_first views over every block, the rest over the compacted survivors), and the persistent kernel that
+// three launches: the first n_first views over every block, the rest over the compacted survivors, then the work list
+// of the blocks still alive in Morton order of the block coordinates (live_order = 1) or row-major order (0)), and the persistent kernel that
 // carves the patches of the surviving blocks (n_ctas = SM count x carve_items_ctas_per_sm()).
 void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
 void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
-                 int n_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
+                 int n_first, int live_order, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
 int carve_items_ctas_per_sm();
 void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
                  const uint2 *live, uint32_t *counters, unsigned long long *work_total);

@@ -29,6 +29,12 @@ bool carve_cull_enabled() {
     return !e || std::atoi(e) != 0;
 }
 
+// BP_LIVE_ORDER=0: work list of the carve in row-major block order instead of Morton order (A/B; see compact_live_kernel).
+bool live_order_morton() {
+    const char *e = std::getenv("BP_LIVE_ORDER");
+    return !e || std::atoi(e) != 0;
+}
+
 // Two-tier masks (device-resident uint8 masks only): the first BP_PACK_HEAD views of a launch, in visiting order, are
 // bit-packed; the later ones are read in place by the few voxels that survive the first (see bp_kernels.cu).
 // Negative = pack every view.  Default 16: measured on C5 (profiles/r02_cull_packhead_ab.txt; the raw reads cost the
@@ -146,10 +152,10 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
         CU(cudaMemcpyAsync(h->cull_views_d, cv, sizeof(CullView) * (size_t)n_cull, cudaMemcpyHostToDevice, h->stream));
     }
     CU(cudaMemsetAsync(h->cull_counters, 0, 4 * sizeof(uint32_t), h->stream));
-    bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, kCullFirstViews, h->blk_dead, h->blk_cand,
-                     h->blk_live, h->cull_counters);
+    bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, kCullFirstViews, live_order_morton() ? 1 : 0,
+                     h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
     CU(cudaGetLastError());
-    h->launches += 1;
+    h->launches += (n_cull > kCullFirstViews) ? 2 : 1;
     bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
                      h->cull_counters, work);
     h->launches += 1;  // (the caller counts the carve launch itself)

@@ -64,6 +64,29 @@ def decode_carve_state(state, default_value=0):
     return out
 
 
+def spread_order(cams):
+    """Farthest-point order of the views' optical axes (rows 10..12 of the 16-float camera rows; a view and its antipode
+    count as one direction): the order the library itself visits the views of a carving launch in (bp_process.cu).
+    Starts at view 0; every next view is the one whose axis is farthest from all chosen so far."""
+    cams = np.asarray(cams, dtype=np.float64).reshape(-1, 16)
+    n = len(cams)
+    if n == 0:
+        return []
+    ax = cams[:, 10:13]
+    norm = np.linalg.norm(ax, axis=1, keepdims=True)
+    ax = np.divide(ax, norm, out=np.zeros_like(ax), where=norm > 0)
+    far = np.full(n, 2.0)
+    used = np.zeros(n, dtype=bool)
+    order, cur = [], 0
+    for _ in range(n):
+        order.append(cur)
+        used[cur] = True
+        far = np.minimum(far, 1.0 - np.abs(ax @ ax[cur]))
+        cand = np.where(used, -1.0, far)
+        cur = int(np.argmax(cand))
+    return order
+
+
 def bind_to_gpu_numa_node(device):
     """Pin this process (and therefore its first-touch / pinned host allocations) to the CPUs NVML reports as
     local to CUDA device ``device``.  With one rank per GPU, host<->device copies then stay on the GPU's own
@@ -204,21 +227,32 @@ class DistributedBackprojection(object):
         n, G, r = len(masks), self.world, self.rank
         carving = self.type == "carving"
         stride = self.local.packed_size(H, W) if carving else ((H * W + 255) // 256) * 256
-        # carving: one chunk per 256 views (the pack + carve of a chunk sweeps the slab once, and there is no
-        # compute worth hiding the upload behind); averaging: ~CHUNK_BYTES of maps, upload hidden behind the kernel
-        per_chunk = 256 if carving else max(1, self.CHUNK_BYTES // (H * W))
-        per_chunk = min(n, max(G, (per_chunk // G) * G))  # a multiple of G, at most n
-        n_per = (per_chunk + G - 1) // G
+        cams = np.ascontiguousarray(cams, dtype=np.float32).reshape(n, 16)
+        spec = carving and bool(getattr(self.local, "speculative_readback", False)) and hasattr(self.local, "spec_snapshot")
+        if carving:
+            # carving is order-independent: visit the views in farthest-point order of their optical axes (the first
+            # few remove almost all empty space), in TWO chunks - after the first, the volume as it stands starts its
+            # way to the host (speculative read-back) under the upload / exchange / carve of the second
+            order = spread_order(cams)
+            cams = cams[order]
+            masks = [masks[v] for v in order]
+            head = min(n, -(-32 // G) * G)
+            bounds = [0, head, n] if (spec and head < n) else [0, n]
+        else:
+            # averaging: ~CHUNK_BYTES of maps per chunk, upload hidden behind the kernel; the caller's view order is kept
+            per_chunk = max(1, self.CHUNK_BYTES // (H * W))
+            per_chunk = min(n, max(G, (per_chunk // G) * G))  # a multiple of G, at most n
+            bounds = list(range(0, n, per_chunk)) + [n]
+        n_per = max((b - a + G - 1) // G for a, b in zip(bounds[:-1], bounds[1:]))
         bufs = self._exchange_buffers(n_per, stride)
         dev = bufs[0].device
         cur = torch.cuda.current_stream(dev)
         eng = torch.cuda.ExternalStream(self.local.stream(), device=dev)
-        hw = np.tile(np.array([[H, W]], dtype=np.int32), (per_chunk, 1))
         done = [None, None]  # event after the pass that last read each buffer
-        for ci, c0 in enumerate(range(0, n, per_chunk)):
-            c1 = min(n, c0 + per_chunk)
+        for ci, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
             buf = bufs[ci & 1]
             mine = list(range(c0 + r, c1, G))
+            hw = np.tile(np.array([[H, W]], dtype=np.int32), (c1 - c0, 1))
             if done[ci & 1] is not None:
                 cur.wait_event(done[ci & 1])      # NCCL / copies must not overwrite what a pass still reads
             if carving:
@@ -227,7 +261,7 @@ class DistributedBackprojection(object):
                 # projects into (BP_VIEW_RECT=0 switches that off)
                 rect = os.environ.get("BP_VIEW_RECT", "1") not in ("", "0")
                 self.local.pack_views([masks[v] for v in mine], buf[r].data_ptr(), stride, invert=invert,
-                                      **({"cams": np.asarray(cams, dtype=np.float32).reshape(-1, 16)[mine]} if rect else {}))
+                                      **({"cams": cams[mine]} if rect else {}))
                 ev = torch.cuda.Event()
                 ev.record(eng)
                 cur.wait_event(ev)
@@ -242,9 +276,11 @@ class DistributedBackprojection(object):
             base = buf.data_ptr()
             ptrs = [base + (((v - c0) % G) * n_per + (v - c0) // G) * stride for v in range(c0, c1)]
             if carving:
-                self.local.process_packed_views(cams[c0:c1], ptrs, hw[:c1 - c0])
+                self.local.process_packed_views(cams[c0:c1], ptrs, hw)
+                if spec and ci == 0 and len(bounds) > 2:
+                    self.local.spec_snapshot()
             else:
-                self.local.process_device_views(cams[c0:c1], ptrs, hw[:c1 - c0], invert=invert)
+                self.local.process_device_views(cams[c0:c1], ptrs, hw, invert=invert)
             done[ci & 1] = torch.cuda.Event()
             done[ci & 1].record(eng)
         for ev in done:                            # host masks are not retained past the call
