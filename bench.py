@@ -556,11 +556,25 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
                 "evaluated_fraction": float(ev) / nominal if nominal else None,
                 "cull_blocks": int(blocks), "cull_blocks_dead": int(dead), "scope": "rank 0, one step"}
 
+    elif hasattr(eng, "work_stats"):
+        # averaging has no early exit; view skipping replaces whole (block, view) pairs by one add
+        eng.sync()
+        eng.work_stats()
+        step_resident()
+        eng.sync()
+        ev, blocks, _ = eng.work_stats()
+        nominal = float(len(my_planes)) * ny * nz * n_views * n_labels
+        work = {"nominal_voxel_views": nominal, "evaluated_voxel_views": float(ev),
+                "evaluated_fraction": float(ev) / nominal if nominal else None, "skip_blocks": int(blocks),
+                "scope": "this rank, one step, all labels"}
+
     # ---- roofline of the dominant kernel(s): the binding resource is the FP32 issue rate, not HBM
     peak_hbm, peak_src = peaks()
     k_ms = float(tmax[1]) / steps / n_labels      # per launch group (all views of one label)
     n_local = len(my_planes)
-    evaluated = work["evaluated_voxel_views"] if work else float(n_local) * ny * nz * n_views
+    evaluated = float(n_local) * ny * nz * n_views
+    if work:
+        evaluated = work["evaluated_voxel_views"] / (n_labels if mode == "averaging" else 1)
     sm_hz = (clk["sm_mhz"] if clk and clk.get("sm_mhz") else 1965.0) * 1e6
     issue_peak = N_SM * 4 * sm_hz / 1e9           # G warp-instructions / s
     useful = evaluated * PRESCRIBED_INSTR / 32.0  # warp-instructions of prescribed arithmetic, this rank, one label
@@ -574,10 +588,11 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
     gbps = (lambda b: b / (k_ms * 1e-3) / 1e9 / peak_hbm) if k_ms > 0 else (lambda b: None)
     roofline = {
         "bound": "issue",
-        "kernel": "cull_blocks_kernel + carve_items_kernel (+ tile_any / tile_sat)" if mode == "carving" else "average_kernel<u8>",
+        "kernel": "cull_blocks_kernel + carve_items_kernel (+ tile_any / tile_sat)" if mode == "carving"
+                  else "average_kernel<u8> (+ map_any / tile_sat / avg_skip)",
         "achieved": achieved, "peak": issue_peak, "unit": "G warp-instr/s", "frac": achieved / issue_peak,
         "definition": f"achieved = voxel-view projections the kernels evaluated "
-                      f"({'counted by the BP_COUNT_WORK variant' if work else 'all of them: averaging has no early exit'}) "
+                      f"({'counted by the BP_COUNT_WORK variant' if mode == 'carving' else 'all voxel-views minus the ones view skipping replaced by one add'}) "
                       f"x {PRESCRIBED_INSTR:.0f} FP32 instructions the reference's arithmetic costs per voxel-view / 32 lanes / "
                       f"kernel time; peak = {N_SM} SMs x 4 schedulers x SM clock under load",
         "traffic": traffic, "kernel_ms_per_launch": k_ms, "ingest_ms_per_step": float(tmax[2]) / steps,

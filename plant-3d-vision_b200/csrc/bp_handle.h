@@ -52,7 +52,12 @@ struct bp_handle {
     size_t sat_bytes = 0;
     int items_ctas = 0;                 // persistent grid of carve_items_kernel
     bool count_work = false;            // BP_COUNT_WORK=1: count the projections the carve kernels evaluate
-    unsigned long long *work_d = nullptr;
+    unsigned long long *work_d = nullptr;  // carving: projections evaluated; averaging: voxel-views skipped
+    // view skipping of the averaging path (bp_kernels.cu: avg_skip_kernel); NULL for carving handles
+    uint32_t *avg_skip_d = nullptr;     // kSkipWords words per skip block
+    int avg_nbj = 0, avg_nbk = 0;
+    uint32_t avg_nblocks = 0;
+    int64_t avg_nominal_vv = 0;         // voxel-views of the averaging launches since the last bp_work_stats
     // speculative read-back (bp_set_readback_target; carving, host masks in several chunks)
     void *spec_target = nullptr;      // pinned host volume the next bp_get_values will be given
     void *spec_target_dev = nullptr;  // the same memory as the device addresses it

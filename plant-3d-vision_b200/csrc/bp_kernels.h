@@ -15,7 +15,8 @@ void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewP
            unsigned long long *work_total);
 // block cull of the carve path: summed-area tables of "tile has a foreground bit" for the views of `jobs`
 // (two launches), the cull itself (dead flags, zero fill of the blocks it kills, work list of the survivors;
-// counters = {live blocks, next work item, blocks killed, candidates after the first pass}, zeroed by the caller;
+// counters (8 words, zeroed by the caller) = {live blocks listed from the front, next work item, blocks killed,
+// candidates after the first pass, live blocks listed from the back};
 // three launches: the first n_first views over every block, the rest over the compacted survivors, then the work list
 // of the blocks still alive in Morton order of the block coordinates (live_order = 1) or row-major order (0)), and the persistent kernel that
 // carves the patches of the surviving blocks (n_ctas = SM count x carve_items_ctas_per_sm()).
@@ -24,9 +25,17 @@ void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGr
                  int n_first, int live_order, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
 int carve_items_ctas_per_sm();
 void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
-                 const uint2 *live, uint32_t *counters, unsigned long long *work_total);
+                 const uint2 *live, uint32_t n_blocks, uint32_t *counters, unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
-void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g);
+// skip (u8 maps only, may be NULL): one bit per (skip block, view) from avg_skip - the view adds c0 to every voxel
+void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g,
+             const uint32_t *skip, int skip_nbj, int skip_nbk, float c0);
+// view skipping of the averaging path: per-tile "holds a byte != B" flags of row-major uint8 maps, their summed-area
+// tables (tile_sat_only: the second half of tile_sat), and the (block, view) skip bits
+void map_any(cudaStream_t st, const MapAnyJobs &jobs, int tiles_y_max);
+void tile_sat_only(cudaStream_t st, const SatJobs &jobs);
+void avg_skip(cudaStream_t st, const GridInfo &g, int nbj, int nbk, uint32_t n_blocks, const CullView *views, int n_views,
+              uint32_t *skip, unsigned long long *skipped);
 // mask ingest: one view of any dtype / width -> 32x32-pixel bit tiles
 void pack_bits(cudaStream_t st, int dtype, const void *src, uint32_t *out, int H, int W, int tpr, int Hpad, uint32_t flags);
 // mask ingest, batched fast path (uint8, 16-byte aligned rows): every view of a chunk in one launch

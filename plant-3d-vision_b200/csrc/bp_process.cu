@@ -37,12 +37,17 @@ bool live_order_morton() {
 
 // Two-tier masks (device-resident uint8 masks only): the first BP_PACK_HEAD views of a launch, in visiting order, are
 // bit-packed; the later ones are read in place by the few voxels that survive the first (see bp_kernels.cu).
-// Negative = pack every view.  Default 16: measured on C5 (profiles/r02_cull_packhead_ab.txt; the raw reads cost the
-// kernel ~0.5 ms whatever the head, the pack 0.004 ms per view).
-int pack_head_views() {
+// Negative = pack every view.  Default: see below.
+int pack_head_views(const bp_handle *h) {
     const char *e = std::getenv("BP_PACK_HEAD");
-    const int v = e ? std::atoi(e) : 16;
-    return v < 0 ? kMaxViews : v;
+    if (e) {
+        const int v = std::atoi(e);
+        return v < 0 ? kMaxViews : v;
+    }
+    // The raw reads cost the kernel in proportion to the voxels the handle holds (~1.0 ms for all of C5), the pack is
+    // the same 0.67 ms whatever the share: a handle that holds (most of) the grid packs everything, a plane-sharded
+    // one packs 16 views (profiles/r02_live_order_ab.txt, r02_cull_packhead_ab.txt).
+    return (3ll * h->g.ni > 2ll * h->shape[0]) ? kMaxViews : 16;
 }
 
 // bit-pack ONE view whose raw mask already sits in device memory (general path: any dtype / width)
@@ -151,14 +156,85 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
         h->launches += 2;
         CU(cudaMemcpyAsync(h->cull_views_d, cv, sizeof(CullView) * (size_t)n_cull, cudaMemcpyHostToDevice, h->stream));
     }
-    CU(cudaMemsetAsync(h->cull_counters, 0, 4 * sizeof(uint32_t), h->stream));
+    CU(cudaMemsetAsync(h->cull_counters, 0, 8 * sizeof(uint32_t), h->stream));
     bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, kCullFirstViews, live_order_morton() ? 1 : 0,
                      h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
     CU(cudaGetLastError());
     h->launches += (n_cull > kCullFirstViews) ? 2 : 1;
     bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
-                     h->cull_counters, work);
+                     h->cg.n_blocks, h->cull_counters, work);
     h->launches += 1;  // (the caller counts the carve launch itself)
+    return BP_OK;
+}
+
+// BP_AVG_SKIP=0 switches the view skipping of the averaging path off (A/B).  Default on.
+bool avg_skip_enabled() {
+    const char *e = std::getenv("BP_AVG_SKIP");
+    return !e || std::atoi(e) != 0;
+}
+
+// View skipping for one averaging launch over uint8 maps (bp_kernels.cu): per view the summed-area table of "tile holds a
+// byte != B", then one skip bit per (block, view).  B = the raw byte whose table entry is the value of a zero pixel
+// (255 under BP_FLAG_INVERT, else 0): the commonest byte of a probability map.  Returns skip == NULL (nothing skipped)
+// when a map does not have 16-byte rows.
+int launch_avg_skip(bp_handle *h, const Batch &batch, const int32_t *hw, const int *order, const float *cams, uint32_t flags,
+                    const uint32_t **skip_out, float *c0_out) {
+    static thread_local SatJobs sat;
+    static thread_local MapAnyJobs any;
+    static thread_local CullView cv[kMaxViews];
+    const int n = batch.n;
+    size_t need = 0;
+    int tiles_y_max = 0;
+    any.tpr_max = 0;
+    for (int q = 0; q < n; ++q) {
+        const int v = order[q], H = hw[2 * v], W = hw[2 * v + 1];
+        if ((W % 16) != 0 || ((uintptr_t)batch.v[q].map % 16) != 0) return BP_OK;
+        const TiledDims d = tiled_dims(H, W);
+        need += (((size_t)(d.tiles_y + 1) * (d.tpr + 1) * 4 + 255) & ~(size_t)255) + (((size_t)d.tiles_y * d.tpr + 255) & ~(size_t)255);
+        if (d.tiles_y > tiles_y_max) tiles_y_max = d.tiles_y;
+        if (d.tpr > any.tpr_max) any.tpr_max = d.tpr;
+    }
+    int rc = ensure(&h->sat_pool, &h->sat_bytes, need, h->stream);
+    if (rc) return rc;
+    const uint32_t B = (flags & BP_FLAG_INVERT) ? 255u : 0u;
+    any.n = sat.n = n;
+    any.b4 = B * 0x01010101u;
+    any.pad = 0;
+    char *pool = (char *)h->sat_pool;
+    for (int q = 0; q < n; ++q) {
+        const int v = order[q], H = hw[2 * v], W = hw[2 * v + 1];
+        const TiledDims d = tiled_dims(H, W);
+        SatJob &J = sat.j[q];
+        J.tiles = nullptr;
+        J.sat = (uint32_t *)pool;
+        pool += ((size_t)(d.tiles_y + 1) * (d.tpr + 1) * 4 + 255) & ~(size_t)255;
+        J.any = (uint8_t *)pool;
+        pool += ((size_t)d.tiles_y * d.tpr + 255) & ~(size_t)255;
+        J.tpr = d.tpr;
+        J.tiles_y = d.tiles_y;
+        MapAnyJob &A = any.j[q];
+        A.src = (const uint8_t *)batch.v[q].map;
+        A.any = J.any;
+        A.H = H;
+        A.W = W;
+        CullView &V = cv[q];
+        for (int a = 0; a < 16; ++a) V.cam[a] = cams[16 * (size_t)v + a];
+        V.sat = J.sat;
+        V.tpr1 = d.tpr + 1;
+        V.W = W;
+        V.H = H;
+        V.pad[0] = V.pad[1] = V.pad[2] = 0;
+    }
+    bpk::map_any(h->stream, any, tiles_y_max);
+    bpk::tile_sat_only(h->stream, sat);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h->cull_views_d, cv, sizeof(CullView) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemsetAsync(h->avg_skip_d, 0, (size_t)h->avg_nblocks * kSkipWords * sizeof(uint32_t), h->stream));
+    bpk::avg_skip(h->stream, h->g, h->avg_nbj, h->avg_nbk, h->avg_nblocks, h->cull_views_d, n, h->avg_skip_d, h->work_d);
+    CU(cudaGetLastError());
+    h->launches += 3;
+    *skip_out = h->avg_skip_d;
+    *c0_out = h->lut_h[B];
     return BP_OK;
 }
 
@@ -300,7 +376,7 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
         // two-tier masks: which views of this launch are read raw (device-resident uint8 masks past the packed head)
         raw_view.assign(nb, 0);
         if (carving && !pack_only && !packed_in && !host_masks && mask_dtype == BP_MASK_U8) {
-            const int head = pack_head_views();
+            const int head = pack_head_views(h);
             for (int q = head; q < nb; ++q) {
                 const int v = order[v0 + q];
                 raw_view[q] = ((size_t)hw[2 * v] * (size_t)hw[2 * v + 1] < ((size_t)1 << 32)) ? 1 : 0;  // 32-bit byte offsets
@@ -444,7 +520,15 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
                 bpk::carve(grd, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, work);
             }
         } else {
-            bpk::average(grd, h->stream, mask_dtype == BP_MASK_U8, (float *)h->grid, h->lut_d, batch, h->g);
+            const uint32_t *skip = nullptr;
+            float c0 = 0.f;
+            if (mask_dtype == BP_MASK_U8 && h->avg_skip_d && !batch.force_exact && avg_skip_enabled()) {
+                rc = launch_avg_skip(h, batch, hw, order.data() + v0, cams, flags, &skip, &c0);
+                if (rc) return rc;
+            }
+            h->avg_nominal_vv += (int64_t)h->g.ni * h->g.ny * h->g.nz * (int64_t)batch.n;
+            bpk::average(grd, h->stream, mask_dtype == BP_MASK_U8, (float *)h->grid, h->lut_d, batch, h->g, skip, h->avg_nbj,
+                         h->avg_nbk, c0);
         }
         CU(cudaGetLastError());
         CU(cudaEventRecord(k1, h->stream));

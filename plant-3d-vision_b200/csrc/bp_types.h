@@ -68,7 +68,6 @@ struct GridInfo {
 // A cull block is kBlkI planes x kBlkJ rows x kBlkK voxels = 16 warp patches of 4 (j) x 32 (k) voxels in one plane.
 constexpr int kBlkI = 8, kBlkJ = 8, kBlkK = 32;
 constexpr int kItemsPerBlock = kBlkI * (kBlkJ / 4) * (kBlkK / 32);
-constexpr int kItemsPerGrab = 4;   // warp patches a warp takes from the work list per atomic
 constexpr int kCullViews = 32;     // views (in visiting order) the block cull may use
 constexpr int kCullFirstViews = 3; // ... of which the first pass (every block) takes these; the rest see survivors only
 
@@ -90,7 +89,29 @@ struct SatJob {  // 32 bytes: build the summed-area table of one view's bit tile
 struct SatJobs {
     int n;
     int pad[3];
-    SatJob j[kCullViews];
+    SatJob j[kMaxViews];
+};
+
+// ------------------------------------------------------------------------------------------
+// view skipping of the averaging path (avg_skip_kernel / average_kernel)
+// ------------------------------------------------------------------------------------------
+// A skip block is kAvgBlkI planes x 32 rows x 64 voxels: the CTA tiles of average_kernel at the same (j, k) tile in 8
+// consecutive planes.  One bit per (block, view of the launch): every voxel of the block lands inside the picture on a
+// pixel holding the launch's "uniform byte", so the view adds the same table entry to all of them.
+constexpr int kAvgBlkI = 8, kAvgBlkJ = 32, kAvgBlkK = 8 * kAvgVpt;
+constexpr int kSkipWords = kMaxViews / 32;
+
+struct MapAnyJob {  // 24 bytes: "does this 32 x 32-pixel tile of a row-major uint8 map hold a byte != B"
+    const uint8_t *src;
+    uint8_t *any;          // tiles_y x tpr
+    int32_t H, W;
+};
+struct MapAnyJobs {
+    int n;
+    int tpr_max;
+    uint32_t b4;           // the uniform byte B replicated four times
+    int pad;
+    MapAnyJob j[kMaxViews];
 };
 
 struct CullGrid {

@@ -244,3 +244,73 @@ def test_counted_work_drops_with_the_cull(BP, monkeypatch):
             bp.close()
     nominal = int(np.prod(w["shape"])) * len(views)
     assert 0 < work[1] < work[0] <= nominal * 1.01  # (padding lanes may count a little)
+
+
+# ---------------------------------------------------------------------------------------------
+# view skipping of the averaging path (avg_skip_kernel): exact by construction, checked bit for bit
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("log", [False, True])
+@pytest.mark.parametrize("invert", [False, True])
+def test_averaging_view_skipping_is_bit_exact(BP, Oracle, log, invert):
+    """Sparse probability maps (mostly one byte value): whole (block, view) pairs are replaced by `sum += table[B]`.
+    Same float32 sums, in the same view order, as the oracle and as the same library with BP_AVG_SKIP=0 - for hard and
+    soft maps, log on / off, plain and inverted readings, and the fused task tail."""
+    from plant3dvision_b200 import synth
+    w = synth.workload("C5", 0.125)
+    masks = synth.render_masks(w["cams"], w["capsules"], w["H"], w["W"], soft_px=2.0).numpy()
+    if invert:
+        masks = np.invert(masks)
+    views = [(*split_cam(w["cams"][v]), masks[v]) for v in range(0, len(w["cams"]), 2)]
+    ora = Oracle(w["shape"], w["origin"], w["voxel_size"], type="averaging", log=log, default_value=0.25)
+    for (i, r, t, m) in views:
+        ora.process_view(i, r, t, np.invert(m) if invert else m)
+    want = ora.get_values()
+    got = {}
+    for skip in (1, 0):
+        with env(BP_AVG_SKIP=skip):
+            bp = BP(w["shape"], w["origin"], w["voxel_size"], type="averaging", log=log, default_value=0.25)
+            bp.process_views(views, invert=invert)
+            got[skip] = bp.get_values().copy()
+            evaluated, blocks, _ = bp.work_stats()
+            bp.close()
+        nominal = int(np.prod(w["shape"])) * len(views)
+        if skip:
+            assert blocks > 0 and 0 < evaluated < 0.9 * nominal, f"only {nominal - evaluated} of {nominal} voxel-views skipped"
+        else:
+            assert evaluated == nominal
+    np.testing.assert_array_equal(got[1], want)
+    np.testing.assert_array_equal(got[0], want)
+
+
+def test_averaging_view_skipping_shapes_and_device_maps(BP, Oracle):
+    """Grids that are not whole skip blocks (8 x 32 x 64 voxels), stripes, device-resident maps, maps whose rows are
+    not 16-byte multiples (no skipping there, same result)."""
+    import torch
+    from plant3dvision_b200 import synth
+    w = synth.workload("C5", 0.1)
+    for (H, W) in ((w["H"], w["W"]), (w["H"] - 3, w["W"] - 5)):
+        masks = synth.render_masks(w["cams"], w["capsules"], H, W, soft_px=1.5).numpy()[::3]
+        cams = w["cams"][::3]
+        views = [(*split_cam(cams[v]), masks[v]) for v in range(len(cams))]
+        for shape in (w["shape"], [w["shape"][0] - 3, 37, 70], [5, 33, 65]):
+            ora = Oracle(shape, w["origin"], w["voxel_size"], type="averaging", log=True)
+            for v in views:
+                ora.process_view(*v)
+            want = ora.get_values()
+            bp = BP(shape, w["origin"], w["voxel_size"], type="averaging", log=True)
+            bp.process_views(views)
+            np.testing.assert_array_equal(bp.get_values(), want, err_msg=f"host maps {H}x{W} {shape}")
+            bp.clear()
+            md = torch.from_numpy(masks.copy()).cuda()
+            hw = np.tile(np.array([[H, W]], dtype=np.int32), (len(cams), 1))
+            bp.process_device_views(cams.astype(np.float32), [md[v].data_ptr() for v in range(len(cams))], hw)
+            np.testing.assert_array_equal(bp.get_values(), want, err_msg=f"device maps {H}x{W} {shape}")
+            bp.close()
+    got = np.zeros_like(want)
+    for rank in range(3):
+        s = BP(shape, w["origin"], w["voxel_size"], type="averaging", log=True, stripes=(1, 3, rank))
+        s.process_views(views)
+        if len(s.planes):
+            got[s.planes] = s.get_values()
+        s.close()
+    np.testing.assert_array_equal(got, want)
