@@ -22,10 +22,10 @@ void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewP
 // carves the patches of the surviving blocks (n_ctas = SM count x carve_items_ctas_per_sm()).
 void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
 void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
-                 int n_first, int live_order, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
+                 int n_first, int live_order, int heavy_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
 int carve_items_ctas_per_sm();
 void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
-                 const uint2 *live, uint32_t n_blocks, uint32_t *counters, unsigned long long *work_total);
+                 const uint2 *live, uint32_t n_blocks, int grab, uint32_t *counters, unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
 // skip (u8 maps only, may be NULL): one bit per (skip block, view) from avg_skip - the view adds c0 to every voxel
 void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g,

@@ -29,6 +29,17 @@ bool carve_cull_enabled() {
     return !e || std::atoi(e) != 0;
 }
 
+int env_int(const char *name, int dflt) {
+    const char *e = std::getenv(name);
+    return e ? std::atoi(e) : dflt;
+}
+
+// BP_ITEM_GRAB = 1 | 2 | 4 | 8 | 16: consecutive patches of one block a warp of carve_items_kernel takes per atomic (A/B)
+int item_grab() {
+    const int g = env_int("BP_ITEM_GRAB", 1);
+    return (g == 1 || g == 2 || g == 4 || g == 8 || g == 16) ? g : 1;
+}
+
 // BP_LIVE_ORDER=0: work list of the carve in row-major block order instead of Morton order (A/B; see compact_live_kernel).
 bool live_order_morton() {
     const char *e = std::getenv("BP_LIVE_ORDER");
@@ -158,11 +169,11 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
     }
     CU(cudaMemsetAsync(h->cull_counters, 0, 8 * sizeof(uint32_t), h->stream));
     bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, kCullFirstViews, live_order_morton() ? 1 : 0,
-                     h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
+                     env_int("BP_LPT", 1), h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
     CU(cudaGetLastError());
     h->launches += (n_cull > kCullFirstViews) ? 2 : 1;
     bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
-                     h->cg.n_blocks, h->cull_counters, work);
+                     h->cg.n_blocks, item_grab(), h->cull_counters, work);
     h->launches += 1;  // (the caller counts the carve launch itself)
     return BP_OK;
 }

@@ -256,7 +256,7 @@ def test_averaging_view_skipping_is_bit_exact(BP, Oracle, log, invert):
     Same float32 sums, in the same view order, as the oracle and as the same library with BP_AVG_SKIP=0 - for hard and
     soft maps, log on / off, plain and inverted readings, and the fused task tail."""
     from plant3dvision_b200 import synth
-    w = synth.workload("C5", 0.125)
+    w = synth.workload("C5", 0.128)  # 768 x 512 maps: 16-byte rows (the batched tile scan needs them)
     masks = synth.render_masks(w["cams"], w["capsules"], w["H"], w["W"], soft_px=2.0).numpy()
     if invert:
         masks = np.invert(masks)
@@ -287,7 +287,7 @@ def test_averaging_view_skipping_shapes_and_device_maps(BP, Oracle):
     not 16-byte multiples (no skipping there, same result)."""
     import torch
     from plant3dvision_b200 import synth
-    w = synth.workload("C5", 0.1)
+    w = synth.workload("C5", 0.096)  # 576 x 384 maps
     for (H, W) in ((w["H"], w["W"]), (w["H"] - 3, w["W"] - 5)):
         masks = synth.render_masks(w["cams"], w["capsules"], H, W, soft_px=1.5).numpy()[::3]
         cams = w["cams"][::3]
