@@ -55,7 +55,7 @@ struct bp_handle {
     unsigned long long *work_d = nullptr;  // carving: projections evaluated; averaging: voxel-views skipped
     // view skipping of the averaging path (bp_kernels.cu: avg_skip_kernel); NULL for carving handles
     uint32_t *avg_skip_d = nullptr;     // kSkipWords words per skip block
-    int avg_nbj = 0, avg_nbk = 0;
+    int avg_nbj = 0, avg_nbk = 0, avg_lgk = 4;  // skip blocks along j / k, log2 of their extent along k
     uint32_t avg_nblocks = 0;
     int64_t avg_nominal_vv = 0;         // voxel-views of the averaging launches since the last bp_work_stats
     // speculative read-back (bp_set_readback_target; carving, host masks in several chunks)

@@ -29,13 +29,13 @@ void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, con
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
 // skip (u8 maps only, may be NULL): one bit per (skip block, view) from avg_skip - the view adds c0 to every voxel
 void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g,
-             const uint32_t *skip, int skip_nbj, int skip_nbk, float c0);
+             const uint32_t *skip, int skip_nbj, int skip_nbk, int skip_lgk, float c0);
 // view skipping of the averaging path: per-tile "holds a byte != B" flags of row-major uint8 maps, their summed-area
 // tables (tile_sat_only: the second half of tile_sat), and the (block, view) skip bits
 void map_any(cudaStream_t st, const MapAnyJobs &jobs, int tiles_y_max);
 void tile_sat_only(cudaStream_t st, const SatJobs &jobs);
-void avg_skip(cudaStream_t st, const GridInfo &g, int nbj, int nbk, uint32_t n_blocks, const CullView *views, int n_views,
-              uint32_t *skip, unsigned long long *skipped);
+void avg_skip(cudaStream_t st, const GridInfo &g, int nbj, int nbk, int lgk, uint32_t n_blocks, const CullView *views,
+              int n_views, uint32_t *skip, unsigned long long *skipped);
 // mask ingest: one view of any dtype / width -> 32x32-pixel bit tiles
 void pack_bits(cudaStream_t st, int dtype, const void *src, uint32_t *out, int H, int W, int tpr, int Hpad, uint32_t flags);
 // mask ingest, batched fast path (uint8, 16-byte aligned rows): every view of a chunk in one launch

@@ -241,7 +241,7 @@ int launch_avg_skip(bp_handle *h, const Batch &batch, const int32_t *hw, const i
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(h->cull_views_d, cv, sizeof(CullView) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemsetAsync(h->avg_skip_d, 0, (size_t)h->avg_nblocks * kSkipWords * sizeof(uint32_t), h->stream));
-    bpk::avg_skip(h->stream, h->g, h->avg_nbj, h->avg_nbk, h->avg_nblocks, h->cull_views_d, n, h->avg_skip_d, h->work_d);
+    bpk::avg_skip(h->stream, h->g, h->avg_nbj, h->avg_nbk, h->avg_lgk, h->avg_nblocks, h->cull_views_d, n, h->avg_skip_d, h->work_d);
     CU(cudaGetLastError());
     h->launches += 3;
     *skip_out = h->avg_skip_d;
@@ -539,7 +539,7 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
             }
             h->avg_nominal_vv += (int64_t)h->g.ni * h->g.ny * h->g.nz * (int64_t)batch.n;
             bpk::average(grd, h->stream, mask_dtype == BP_MASK_U8, (float *)h->grid, h->lut_d, batch, h->g, skip, h->avg_nbj,
-                         h->avg_nbk, c0);
+                         h->avg_nbk, h->avg_lgk, c0);
         }
         CU(cudaGetLastError());
         CU(cudaEventRecord(k1, h->stream));

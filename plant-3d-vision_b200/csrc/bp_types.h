@@ -95,10 +95,12 @@ struct SatJobs {
 // ------------------------------------------------------------------------------------------
 // view skipping of the averaging path (avg_skip_kernel / average_kernel)
 // ------------------------------------------------------------------------------------------
-// A skip block is kAvgBlkI planes x 32 rows x 64 voxels: the CTA tiles of average_kernel at the same (j, k) tile in 8
-// consecutive planes.  One bit per (block, view of the launch): every voxel of the block lands inside the picture on a
-// pixel holding the launch's "uniform byte", so the view adds the same table entry to all of them.
-constexpr int kAvgBlkI = 8, kAvgBlkJ = 32, kAvgBlkK = 8 * kAvgVpt;
+// A skip block is kAvgBlkI planes x 32 rows x 2^lgk voxels (lgk = 3..6, bp_handle::avg_lgk): the voxels of 1, 2, 4 or
+// 8 warps of an average_kernel CTA tile, in 8 consecutive planes.  One bit per (block, view of the launch): every voxel
+// of the block lands inside the picture on a pixel holding the launch's "uniform byte", so the view adds the same
+// table entry to all of them.
+constexpr int kAvgBlkI = 8, kAvgBlkJ = 32;
+constexpr int kAvgTileK = 8 * kAvgVpt;          // voxels along k of an average_kernel CTA tile
 constexpr int kSkipWords = kMaxViews / 32;
 
 struct MapAnyJob {  // 24 bytes: "does this 32 x 32-pixel tile of a row-major uint8 map hold a byte != B"

@@ -282,9 +282,11 @@ def test_averaging_view_skipping_is_bit_exact(BP, Oracle, log, invert):
     np.testing.assert_array_equal(got[0], want)
 
 
-def test_averaging_view_skipping_shapes_and_device_maps(BP, Oracle):
-    """Grids that are not whole skip blocks (8 x 32 x 64 voxels), stripes, device-resident maps, maps whose rows are
+@pytest.mark.parametrize("blk_k", [8, 16, 64])
+def test_averaging_view_skipping_shapes_and_device_maps(BP, Oracle, blk_k, monkeypatch):
+    """Grids that are not whole skip blocks (8 x 32 x blk_k voxels), stripes, device-resident maps, maps whose rows are
     not 16-byte multiples (no skipping there, same result)."""
+    monkeypatch.setenv("BP_AVG_BLK_K", str(blk_k))
     import torch
     from plant3dvision_b200 import synth
     w = synth.workload("C5", 0.096)  # 576 x 384 maps
