@@ -46,6 +46,7 @@ struct bp_handle {
     uint8_t *blk_dead = nullptr;        // one byte per cull block, persistent until bp_clear
     uint2 *blk_live = nullptr;          // work list of one launch
     uint2 *blk_cand = nullptr;          // survivors of the cull's first pass
+    uint8_t *patch_cls = nullptr;       // one byte per work item: how alive the patch is after the first views
     uint32_t *cull_counters = nullptr;  // {live blocks, next work item, blocks killed, -}
     CullView *cull_views_d = nullptr;   // kCullViews entries
     void *sat_pool = nullptr;           // summed-area tables (+ scratch) of one launch

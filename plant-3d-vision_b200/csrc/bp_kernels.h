@@ -24,8 +24,15 @@ void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
 void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
                  int n_first, int live_order, int heavy_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
 int carve_items_ctas_per_sm();
+// carve_items walks every patch of the surviving blocks through the first v_split views and leaves one class byte per
+// work item (0 dead .. 3 more than 64 voxels live) in cls; carve_segments cuts the remaining views of the live patches
+// into segments any warp can take (counters[6]), merging the segments of one patch by atomic minimum.
 void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
-                 const uint2 *live, uint32_t n_blocks, int grab, uint32_t *counters, unsigned long long *work_total);
+                 const uint2 *live, uint32_t n_blocks, int grab, int v_split, uint8_t *cls, uint32_t *counters,
+                 unsigned long long *work_total);
+void carve_segments(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
+                    const uint2 *live, uint32_t n_blocks, int v_split, const uint8_t *cls, uint32_t *counters,
+                    unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
 // skip (u8 maps only, may be NULL): one bit per (skip block, view) from avg_skip - the view adds c0 to every voxel
 void average(dim3 grd, cudaStream_t st, bool u8_maps, float *value, const float *lut, const Batch &b, const GridInfo &g,

@@ -172,9 +172,19 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
                      env_int("BP_LPT", 1), h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
     CU(cudaGetLastError());
     h->launches += (n_cull > kCullFirstViews) ? 2 : 1;
+    // the first views over every surviving patch; the remaining views of the patches still alive, cut into segments
+    // that any warp can take (BP_VIEW_SPLIT: where to cut; >= the view count: no second kernel)
+    const int v_split = std::max(1, env_int("BP_VIEW_SPLIT", 16));
     bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
-                     h->cg.n_blocks, item_grab(), h->cull_counters, work);
-    h->launches += 1;  // (the caller counts the carve launch itself)
+                     h->cg.n_blocks, item_grab(), v_split, h->patch_cls, h->cull_counters, work);
+    h->launches += 1;  // (the caller counts the last carve launch itself)
+    if (batch.n > v_split) {
+        CU(cudaGetLastError());
+        bpk::carve_segments(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
+                            h->cg.n_blocks, v_split, h->patch_cls, h->cull_counters, work);
+    } else {
+        h->launches -= 1;
+    }
     return BP_OK;
 }
 
