@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Per-rank cost of the device-resident C5 carving step at world sizes 1 / 2 / 4 / 8, measured on ONE GPU: rank 0's
 striped handle alone (the other ranks do the same work on the same masks - stripes of 8 planes dealt round robin balance
-to a few percent).  Sweeps the scheduling switches of the carve path (BP_ITEM_GRAB, BP_LPT, BP_LIVE_ORDER, BP_PACK_HEAD).
+to a few percent).  Sweeps the scheduling switches of the carve path (BP_ITEM_GRAB, BP_LPT, BP_VIEW_SPLIT; 1000 = no view segments).
 Usage: python tools/stripe_probe.py [worlds, e.g. 1,2,8] > gpurun_out/stripe_probe.txt"""
 import itertools
 import os
@@ -28,13 +28,9 @@ def main():
     ptrs = [masks[v].data_ptr() for v in range(n)]
     cams = w["cams"].astype(np.float32)
     hw = np.tile(np.array([[H, W]], dtype=np.int32), (n, 1))
-    combos = [dict(BP_ITEM_GRAB=g, BP_LPT=l, BP_LIVE_ORDER=o, BP_PACK_HEAD=h)
-              for g, l, o, h in itertools.product((1, 4), (0, 1), (1,), ("auto",))]
-    combos += [dict(BP_ITEM_GRAB=4, BP_LPT=0, BP_LIVE_ORDER=0, BP_PACK_HEAD="auto"),
-               dict(BP_ITEM_GRAB=2, BP_LPT=1, BP_LIVE_ORDER=1, BP_PACK_HEAD="auto"),
-               dict(BP_ITEM_GRAB=4, BP_LPT=0, BP_LIVE_ORDER=1, BP_PACK_HEAD=-1),
-               dict(BP_ITEM_GRAB=4, BP_LPT=0, BP_LIVE_ORDER=1, BP_PACK_HEAD=16)]
-    print("world  grab lpt order head | step_ms kernel_ms ingest_ms")
+    combos = [dict(BP_ITEM_GRAB=g, BP_LPT=l, BP_LIVE_ORDER=1, BP_PACK_HEAD="auto", BP_VIEW_SPLIT=sp)
+              for g, l, sp in ((1, 1, 16), (1, 1, 1000), (4, 1, 16), (2, 1, 16), (1, 0, 16), (1, 1, 8), (1, 1, 32))]
+    print("world  grab lpt split head | step_ms kernel_ms ingest_ms")
     for world in worlds:
         for c in combos:
             for k, v in c.items():
@@ -60,7 +56,7 @@ def main():
             bp.sync()
             torch.cuda.synchronize()
             k_ms, i_ms, _ = bp.timing()
-            print(f"{world:5d}  {c['BP_ITEM_GRAB']:4} {c['BP_LPT']:3} {c['BP_LIVE_ORDER']:5} {str(c['BP_PACK_HEAD']):>4} | "
+            print(f"{world:5d}  {c['BP_ITEM_GRAB']:4} {c['BP_LPT']:3} {c['BP_VIEW_SPLIT']:5} {str(c['BP_PACK_HEAD']):>4} | "
                   f"{e0.elapsed_time(e1) / steps:7.3f} {k_ms / steps:9.3f} {i_ms / steps:9.3f}", flush=True)
             bp.close()
 
