@@ -200,6 +200,55 @@ def test_two_tier_speckle_walks_every_phase_on_raw_masks(BP, Oracle):
     assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ"
 
 
+@pytest.mark.parametrize("split,grab,lpt", [(1, 1, 1), (4, 1, 1), (16, 1, 1), (16, 4, 0), (33, 2, 1), (1000, 1, 0)])
+def test_view_segments_and_scheduling_switches(BP, Oracle, split, grab, lpt):
+    """The views after the first ``BP_VIEW_SPLIT`` of a launch run as segments of the still-live patches that any warp
+    may take (carve_segments_kernel: merged into the state by an atomic byte-wise minimum, carving being order-free);
+    ``BP_ITEM_GRAB`` / ``BP_LPT`` change only who does which patch.  Bit-exact whatever the split, on a scene whose
+    hull voxels meet every view and on speckle masks whose patches decay slowly through every class."""
+    import torch
+    from plant3dvision_b200 import synth
+    w, views = synth_scene("C5", 0.125, n_views=70)
+    want = oracle_volume(Oracle, w, views)
+    w2 = synth.workload("C2", 0.2)
+    rng = np.random.default_rng(11)
+    n = len(w2["cams"])
+    speckle = np.where(rng.random((n, w2["H"], w2["W"])) < 0.03, 0, 255).astype(np.uint8)
+    views2 = [(*split_cam(w2["cams"][v]), speckle[v]) for v in range(n)]
+    want2 = oracle_volume(Oracle, w2, views2)
+    md = torch.from_numpy(speckle).cuda()
+    hw = np.tile(np.array([[w2["H"], w2["W"]]], dtype=np.int32), (n, 1))
+    with env(BP_VIEW_SPLIT=split, BP_ITEM_GRAB=grab, BP_LPT=lpt):
+        bp = BP(w["shape"], w["origin"], w["voxel_size"])
+        bp.process_views(views)
+        got = bp.get_values().copy()
+        bp.close()
+        bp = BP(w2["shape"], w2["origin"], w2["voxel_size"])
+        bp.process_views(views2)
+        got2 = bp.get_values().copy()
+        bp.clear()
+        bp.process_device_views(w2["cams"].astype(np.float32), [md[v].data_ptr() for v in range(n)], hw)
+        got3 = bp.get_values().copy()
+        bp.close()
+    assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ (scene)"
+    assert np.array_equal(got2, want2), f"{(got2 != want2).sum()} voxels differ (speckle, host masks)"
+    assert np.array_equal(got3, want2), f"{(got3 != want2).sum()} voxels differ (speckle, raw device masks)"
+
+
+def test_view_segments_default_value_and_chunks(BP, Oracle):
+    """Segments over several launches of one scan (host masks in chunks of 20 views, split 4) and with a non-zero
+    default: a voxel no view sees must keep the 'unseen' coding through the atomic merge."""
+    w, views = synth_scene("C5", 0.1, n_views=60)
+    one_mask = views[0][3].nbytes
+    for d in (0, -3):
+        want = oracle_volume(Oracle, w, views, default_value=d)
+        with env(BP_VIEW_SPLIT=4, BP_STAGE_BYTES=20 * one_mask):
+            bp = BP(w["shape"], w["origin"], w["voxel_size"], default_value=d)
+            bp.process_views(views)
+            np.testing.assert_array_equal(bp.get_values(), want, err_msg=f"default {d}")
+            bp.close()
+
+
 def test_cull_on_striped_and_slab_handles(BP, Oracle):
     """Plane-sharded handles: a cull block of 8 LOCAL planes spans non-contiguous global planes under stripes narrower
     than a block; the bounds must still contain every voxel."""
