@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libbp_b200.so")
+# BP_B200_LIB: another build of the SAME sources (compile-time A/B variants, tools/build_variants.py) - never a fallback
+LIB_PATH = os.environ.get("BP_B200_LIB") or os.path.join(_PKG, "libbp_b200.so")
 
 MODE_CARVING, MODE_AVERAGING = 0, 1
 MASK_U8, MASK_I32, MASK_F32, MASK_U16 = 0, 1, 2, 3

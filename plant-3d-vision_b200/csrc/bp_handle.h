@@ -51,7 +51,7 @@ struct bp_handle {
     CullView *cull_views_d = nullptr;   // kCullViews entries
     void *sat_pool = nullptr;           // summed-area tables (+ scratch) of one launch
     size_t sat_bytes = 0;
-    int items_ctas = 0;                 // persistent grid of carve_items_kernel
+    int items_ctas = 0;                 // SM count (persistent grids of carve_items / carve_segments = this x occupancy)
     bool count_work = false;            // BP_COUNT_WORK=1: count the projections the carve kernels evaluate
     unsigned long long *work_d = nullptr;  // carving: projections evaluated; averaging: voxel-views skipped
     // view skipping of the averaging path (bp_kernels.cu: avg_skip_kernel); NULL for carving handles

@@ -19,7 +19,7 @@ void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewP
 // candidates after the first pass, live blocks listed from the back};
 // three launches: the first n_first views over every block, the rest over the compacted survivors, then the work list
 // of the blocks still alive in Morton order of the block coordinates (live_order = 1) or row-major order (0)), and the persistent kernel that
-// carves the patches of the surviving blocks (n_ctas = SM count x carve_items_ctas_per_sm()).
+// carves the patches of the surviving blocks (persistent grids: SM count x the occupancy of each kernel).
 void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
 void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
                  int n_first, int live_order, int heavy_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
@@ -27,10 +27,10 @@ int carve_items_ctas_per_sm();
 // carve_items walks every patch of the surviving blocks through the first v_split views and leaves one class byte per
 // work item (0 dead .. 3 more than 64 voxels live) in cls; carve_segments cuts the remaining views of the live patches
 // into segments any warp can take (counters[6]), merging the segments of one patch by atomic minimum.
-void carve_items(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
+void carve_items(int n_sm, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
                  const uint2 *live, uint32_t n_blocks, int grab, int v_split, uint8_t *cls, uint32_t *counters,
                  unsigned long long *work_total);
-void carve_segments(int n_ctas, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
+void carve_segments(int n_sm, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
                     const uint2 *live, uint32_t n_blocks, int v_split, const uint8_t *cls, uint32_t *counters,
                     unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
