@@ -176,10 +176,11 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
     // that any warp can take (BP_VIEW_SPLIT: where to cut; >= the view count: no second kernel)
     const int v_split = std::max(1, env_int("BP_VIEW_SPLIT", 16));
     bpk::carve_items(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
-                     h->cg.n_blocks, item_grab(), v_split, batch.n > v_split ? h->patch_cls : nullptr, h->cull_counters, work);
+                     h->cg.n_blocks, item_grab(), v_split, h->cull_counters, work);
     h->launches += 1;  // (the caller counts the last carve launch itself)
     if (batch.n > v_split) {
         CU(cudaGetLastError());
+        h->launches += 2;  // classify_items_kernel, decode_items_kernel
         bpk::carve_segments(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
                             h->cg.n_blocks, v_split, h->patch_cls, h->cull_counters, work);
     } else {
