@@ -21,7 +21,7 @@ SYMBOLS = [
     "bp_get_values", "bp_get_values_tail", "bp_get_values_device", "bp_device_state", "bp_sync", "bp_stream", "bp_timing",
     "bp_host_alloc", "bp_host_free", "bp_last_error", "bp_version", "bp_selftest_division",
     "bp_pack_views", "bp_packed_size", "bp_create_striped", "bp_ingest_bytes", "bp_view_rect", "bp_pack_views_cams", "bp_set_readback_target", "bp_spec_stats",
-    "bp_work_stats", "bp_box_bounds_host", "bp_spec_snapshot",
+    "bp_work_stats", "bp_box_bounds_host", "bp_spec_snapshot", "bp_tail_static",
 ]
 
 # every symbol include/vol2pcd_b200.h declares (volume -> point-cloud handoff)
@@ -81,6 +81,8 @@ def lib():
                                            ctypes.POINTER(ctypes.c_uint64)]
         L.bp_set_readback_target.argtypes = [vp, vp]
         L.bp_spec_snapshot.argtypes = [vp]
+        L.bp_tail_static.argtypes = [ctypes.c_int, ctypes.c_int, vp, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, c_i,
+                                     ctypes.c_uint32, vp, vp, vp]
         L.bp_spec_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)]
         L.bp_work_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64),
                                     ctypes.POINTER(ctypes.c_int64)]
