@@ -47,6 +47,7 @@ struct bp_handle {
     uint2 *blk_live = nullptr;          // work list of one launch
     uint2 *blk_cand = nullptr;          // survivors of the cull's first pass
     uint8_t *patch_cls = nullptr;       // one byte per work item: how alive the patch is after the first views
+    uint32_t *seg_items = nullptr;      // one word per work item: the live items carve_segments_kernel draws from
     uint32_t *cull_counters = nullptr;  // {live blocks, next work item, blocks killed, -}
     CullView *cull_views_d = nullptr;   // kCullViews entries
     void *sat_pool = nullptr;           // summed-area tables (+ scratch) of one launch

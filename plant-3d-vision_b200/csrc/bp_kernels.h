@@ -26,12 +26,12 @@ void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGr
 int carve_items_ctas_per_sm();
 // carve_items walks every patch of the surviving blocks through the first v_split views; carve_segments (three launches)
 // classifies the patches (one byte per work item in cls: 0 dead .. 3 more than 64 voxels live), cuts the remaining views
-// of the live ones into segments any warp can take (counters[6]), merged by an atomic AND on a transient coding, and
+// of the live ones into segments any warp can take (seg: one uint32 per work item; counters[5..7]), merged by an atomic AND on a transient coding, and
 // restores the coding.  n_sm: SM count - the persistent grids are n_sm x the occupancy of each kernel.
 void carve_items(int n_sm, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
                  const uint2 *live, uint32_t n_blocks, int grab, int v_split, uint32_t *counters, unsigned long long *work_total);
 void carve_segments(int n_sm, cudaStream_t st, int8_t *state, const Batch &b, const ViewParams *gviews, const GridInfo &g,
-                    const uint2 *live, uint32_t n_blocks, int v_split, uint8_t *cls, uint32_t *counters,
+                    const uint2 *live, uint32_t n_blocks, int v_split, uint8_t *cls, uint32_t *seg, uint32_t *counters,
                     unsigned long long *work_total);
 // fused multi-view average (kernels/backprojection.c:36-55); uint8 maps through the 256-entry table, or float32 maps
 // skip (u8 maps only, may be NULL): one bit per (skip block, view) from avg_skip - the view adds c0 to every voxel

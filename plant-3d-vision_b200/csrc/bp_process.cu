@@ -182,7 +182,7 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
         CU(cudaGetLastError());
         h->launches += 2;  // classify_items_kernel, decode_items_kernel
         bpk::carve_segments(h->items_ctas, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, h->blk_live,
-                            h->cg.n_blocks, v_split, h->patch_cls, h->cull_counters, work);
+                            h->cg.n_blocks, v_split, h->patch_cls, h->seg_items, h->cull_counters, work);
     } else {
         h->launches -= 1;
     }
