@@ -5,10 +5,10 @@
 set -e
 R=${1:-r02}
 SO=plant-3d-vision_b200/libbp_b200.so
-for k in carve_items_kernelILb0 cull_blocks_kernel average_kernelIh carve_kernelILb0 pack_bits_u8x16_kernelILi0 tile_any_kernel tile_sat_kernel expand_state_kernel; do
+for k in carve_items_kernelILb0 carve_segments_kernelILb0 classify_items_kernel decode_items_kernel cull_blocks_kernel average_kernelIh carve_kernelILb0 pack_bits_u8x16_kernelILi0 tile_any_kernel tile_sat_kernel expand_state_kernel; do
   out=profiles/${R}_sass_$(echo $k | sed 's/ILb0//; s/ILi0//; s/Ih/_u8/').txt
   cuobjdump -sass $SO | awk -v k=$k '/Function :/{f=($0~k)} f' | sed 's#/\* 0x[0-9a-f]* \*/##; s/[ \t]*$//' | grep -v '^$' > $out
   echo "$out: $(grep -c ';' $out) instructions"
 done
-{ for k in carve_items_kernelILb0 average_kernelIh cull_blocks_kernel; do python tools/sass_loops.py $k 30; done; } > profiles/${R}_sass_loops.txt
+{ for k in carve_items_kernelILb0 carve_segments_kernelILb0 average_kernelIh cull_blocks_kernel; do python tools/sass_loops.py $k 30; done; } > profiles/${R}_sass_loops.txt
 cat profiles/${R}_sass_loops.txt | cut -c1-220
