@@ -633,13 +633,13 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
         for _ in range(2):
             vols = step_e2e()
         barrier()
-        moved0 = eng.ingest_bytes()
+        moved0 = eng.ingest_bytes() + getattr(bp, "h2d_torch_bytes", 0)
         t0 = time.perf_counter()
         for _ in range(steps):
             vols = step_e2e()
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        moved = torch.tensor([float(eng.ingest_bytes() - moved0) / steps], dtype=torch.float64, device=dev)
+        moved = torch.tensor([float(eng.ingest_bytes() + getattr(bp, "h2d_torch_bytes", 0) - moved0) / steps], dtype=torch.float64, device=dev)
         # int32 / float32 volumes; a label stack leaves the device as float64 (the tail kernel widens, cl.py:249)
         d2h = torch.tensor([float(np.asarray(vols).size) * (8 if np.asarray(vols).dtype == np.float64 else 4)],
                            dtype=torch.float64, device=dev)
@@ -649,8 +649,8 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
             dist.all_reduce(d2h, op=dist.ReduceOp.SUM)
         e2e = {"value": total_vv * steps / float(dt[0]), "unit": UNIT, "ms_per_step": 1e3 * float(dt[0]) / steps,
                "h2d_bytes_per_step": int(moved[0]), "d2h_bytes_per_step": int(d2h[0]), "api": api,
-               "h2d_note": "bytes the library copied up (bp_ingest_bytes, all ranks): view rectangles trim each mask to "
-                           "the pixels the grid projects into",
+               "h2d_note": "bytes copied up, all ranks (bp_ingest_bytes + the sharded averaging ingest's own torch copies): view "
+                           "rectangles trim each mask to the pixels the grid projects into",
                "ingest": getattr(bp, "last_ingest", None) or "single GPU"}
         if world == 1 and mode == "carving" and getattr(eng, "speculative_readback", False):
             patched, rows = eng.spec_stats()

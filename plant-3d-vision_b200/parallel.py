@@ -185,6 +185,8 @@ class DistributedBackprojection(object):
         self.ingest = ingest
         self._xbuf = None
         self.last_ingest = None  # how the last process_views call moved the masks
+        self.trace = None  # see _tick
+        self.h2d_torch_bytes = 0  # host -> device bytes this object copied through torch (the library counts its own)
 
     # -- work distribution ---------------------------------------------------------------------
     def my_views(self, n_views):
@@ -208,6 +210,17 @@ class DistributedBackprojection(object):
 
     #: raw mask bytes per pipeline chunk of the sharded ingest
     CHUNK_BYTES = 512 << 20
+    #: views per chunk of the sharded carving ingest after the first 32
+    CARVE_CHUNK_VIEWS = 48
+
+    def _tick(self, label):
+        """Diagnostics (``self.trace = []`` switches it on; never during a timed run): synchronise the device and note the
+        wall clock, so that the phases of the sharded ingest can be timed one by one, un-overlapped (tools/e2e_trace.py)."""
+        if self.trace is not None:
+            import time
+            import torch
+            torch.cuda.synchronize()
+            self.trace.append((label, time.perf_counter()))
 
     def _exchange_buffers(self, n_per, stride):
         import torch
@@ -231,13 +244,19 @@ class DistributedBackprojection(object):
         spec = carving and bool(getattr(self.local, "speculative_readback", False)) and hasattr(self.local, "spec_snapshot")
         if carving:
             # carving is order-independent: visit the views in farthest-point order of their optical axes (the first
-            # few remove almost all empty space), in TWO chunks - after the first, the volume as it stands starts its
-            # way to the host (speculative read-back) under the upload / exchange / carve of the second
+            # few remove almost all empty space).  After the first chunk (32 views) the volume as it stands starts its
+            # way to the host (speculative read-back) under the upload / exchange / carve of the rest, which goes in
+            # chunks of ~CARVE_CHUNK_VIEWS: the host blocks in the upload of chunk c+1 while the all-gather and the
+            # kernels of chunk c run (one chunk for the rest left upload -> all-gather -> kernels in a row: 44 ms
+            # instead of 33 at G = 2, tools/e2e_trace.py)
             order = spread_order(cams)
             cams = cams[order]
             masks = [masks[v] for v in order]
             head = min(n, -(-32 // G) * G)
-            bounds = [0, head, n] if (spec and head < n) else [0, n]
+            step = max(G, (int(os.environ.get("BP_SHARD_CHUNK_VIEWS", self.CARVE_CHUNK_VIEWS)) // G) * G)
+            bounds = ([0] + list(range(head, n, step)) + [n]) if head < n else [0, n]
+            if len(bounds) > 3 and bounds[-1] - bounds[-2] < step // 2:
+                del bounds[-2]  # no short last chunk
         else:
             # averaging: ~CHUNK_BYTES of maps per chunk, upload hidden behind the kernel; the caller's view order is kept
             per_chunk = max(1, self.CHUNK_BYTES // (H * W))
@@ -249,6 +268,7 @@ class DistributedBackprojection(object):
         cur = torch.cuda.current_stream(dev)
         eng = torch.cuda.ExternalStream(self.local.stream(), device=dev)
         done = [None, None]  # event after the pass that last read each buffer
+        self._tick("start")
         for ci, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
             buf = bufs[ci & 1]
             mine = list(range(c0 + r, c1, G))
@@ -269,7 +289,10 @@ class DistributedBackprojection(object):
                 for q, v in enumerate(mine):
                     buf[r, q, :H * W].view(H, W).copy_(torch.from_numpy(np.ascontiguousarray(masks[v])),
                                                        non_blocking=True)
+                self.h2d_torch_bytes += len(mine) * H * W  # uploads the library's own counter does not see
+            self._tick(f"chunk {ci}: upload{' + pack' if carving else ''} of {len(mine)} views")
             dist.all_gather_into_tensor(buf.view(-1), buf[r].reshape(-1), group=self.group)
+            self._tick(f"chunk {ci}: all-gather")
             ev = torch.cuda.Event()
             ev.record(cur)
             eng.wait_event(ev)
@@ -281,6 +304,7 @@ class DistributedBackprojection(object):
                     self.local.spec_snapshot()
             else:
                 self.local.process_device_views(cams[c0:c1], ptrs, hw, invert=invert)
+            self._tick(f"chunk {ci}: kernels on {c1 - c0} views" + (" + early copy of the volume" if spec and ci == 0 and len(bounds) > 2 else ""))
             done[ci & 1] = torch.cuda.Event()
             done[ci & 1].record(eng)
         for ev in done:                            # host masks are not retained past the call
