@@ -263,11 +263,16 @@ def sample_planes(candidates, n):
     return sorted({candidates[int((q + 0.5) * len(candidates) / n)] for q in range(n)})
 
 
-def auto_planes(w, mode):
-    # a few seconds of CPU work on all cores: carving skips carved voxels early, averaging touches every voxel-view
+def auto_planes(w, mode, long_sample=False):
+    """Planes of the CPU sample.  `long_sample` (the timed cpu_baseline of the single-GPU line): about 10 s of work on
+    all cores - carving skips carved voxels early (port: ~16 G vv/s on 16 threads), averaging touches every voxel-view
+    (~1.5 G vv/s); otherwise (the oracle check at N > 1, where torchrun leaves one OpenMP thread per rank) a second or two."""
     per_plane = w["shape"][1] * w["shape"][2] * len(w["cams"]) * (len(w["labels"]) if w["labels"] else 1)
-    budget = 2.4e10 if mode == "carving" else 6e9
-    return int(max(2, min(32, budget // max(per_plane, 1))))
+    if long_sample:
+        budget, cap = (1.6e11, 640) if mode == "carving" else (1.5e10, 64)
+    else:
+        budget, cap = (2.4e10, 32) if mode == "carving" else (6e9, 32)
+    return int(max(2, min(cap, budget // max(per_plane, 1))))
 
 
 def _cpu_lut(log):
@@ -588,7 +593,7 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
     gbps = (lambda b: b / (k_ms * 1e-3) / 1e9 / peak_hbm) if k_ms > 0 else (lambda b: None)
     roofline = {
         "bound": "issue",
-        "kernel": "cull_blocks_kernel + carve_items_kernel (+ tile_any / tile_sat)" if mode == "carving"
+        "kernel": "carve_items_kernel + carve_segments_kernel (+ cull_blocks / classify_items / decode_items / tile_any / tile_sat)" if mode == "carving"
                   else "average_kernel<u8> (+ map_any / tile_sat / avg_skip)",
         "achieved": achieved, "peak": issue_peak, "unit": "G warp-instr/s", "frac": achieved / issue_peak,
         "definition": f"achieved = voxel-view projections the kernels evaluated "
@@ -666,7 +671,7 @@ def measure(args, ctx, w, mode, masks, sharding, with_cpu=True, with_e2e=True, s
         vols_np = np.asarray(vols)
         if vols_np.ndim == 3:
             vols_np = vols_np[None]
-        n_pl = args.cpu_planes or auto_planes(w, mode)
+        n_pl = args.cpu_planes or auto_planes(w, mode, long_sample=(world == 1))
         planes = sample_planes(my_planes, n_pl)
         idx = [my_planes.index(p) for p in planes]
         if world > 1 and sharding == "views":
