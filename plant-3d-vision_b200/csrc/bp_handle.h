@@ -44,6 +44,8 @@ struct bp_handle {
     // a carving handle or its block grid does not fit the 16-bit block coordinates of the work list
     CullGrid cg{};
     uint8_t *blk_dead = nullptr;        // one byte per cull block, persistent until bp_clear
+    bool lazy_unseen = false;           // carving: bp_clear has NOT written the state yet ("all unseen"): the cull's first
+                                        // pass writes every block, anything else that touches the state calls settle_seed
     uint2 *blk_live = nullptr;          // work list of one launch
     uint2 *blk_cand = nullptr;          // survivors of the cull's first pass
     uint8_t *patch_cls = nullptr;       // one byte per work item: how alive the patch is after the first views
@@ -96,6 +98,8 @@ int global_plane_host(const GridInfo &G, int li);
 // speculative read-back: first half (bp_process.cu calls it after the chosen chunk), and the wait that frees outbuf
 int start_spec_readback(bp_handle *h);
 int spec_settle(bp_handle *h);
+// lazy clear: write the pending "all unseen" seed now (no-op when nothing is pending)
+int settle_seed(bp_handle *h);
 
 // carving: 32x32-pixel bit tiles of one view (32 words each) in the pool
 struct TiledDims {

@@ -22,7 +22,8 @@ void carve(dim3 grd, cudaStream_t st, int8_t *state, const Batch &b, const ViewP
 // carves the patches of the surviving blocks (persistent grids: SM count x the occupancy of each kernel).
 void tile_sat(cudaStream_t st, const SatJobs &jobs, int max_tiles);
 void cull_blocks(cudaStream_t st, int8_t *state, const GridInfo &g, const CullGrid &cg, const CullView *views, int n_views,
-                 int n_first, int live_order, int heavy_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters);
+                 int n_first, int live_order, int heavy_first, uint8_t *dead, uint2 *cand, uint2 *live, uint32_t *counters,
+                 bool fill_unseen);  // fill_unseen: the state is unseeded (lazy clear) - the first pass writes every block
 int carve_items_ctas_per_sm();
 // carve_items walks every patch of the surviving blocks through the first v_split views; carve_segments (three launches)
 // classifies the patches (one byte per work item in cls: 0 dead .. 3 more than 64 voxels live), cuts the remaining views

@@ -55,10 +55,12 @@ int pack_head_views(const bp_handle *h) {
         const int v = std::atoi(e);
         return v < 0 ? kMaxViews : v;
     }
-    // The raw reads cost the kernel in proportion to the voxels the handle holds (~1.0 ms for all of C5), the pack is
-    // the same 0.67 ms whatever the share: a handle that holds (most of) the grid packs everything, a plane-sharded
-    // one packs 16 views (profiles/r02_live_order_ab.txt, r02_cull_packhead_ab.txt).
-    return (3ll * h->g.ni > 2ll * h->shape[0]) ? kMaxViews : 16;
+    // 16 views whatever the share of the grid the handle holds: since the later views run as view segments
+    // (carve_segments_kernel) the raw reads cost the kernels nothing measurable (C5, one GPU: kernels 7.07 ms with 16
+    // views packed against 7.12 with all 240, and 0.06 instead of 0.73 ms of packing; with 32 / 64 packed views both
+    // the pack and the tile tables of the cull grow: profiles/r02_packhead_v2.txt).
+    (void)h;
+    return 16;
 }
 
 // bit-pack ONE view whose raw mask already sits in device memory (general path: any dtype / width)
@@ -169,7 +171,8 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
     }
     CU(cudaMemsetAsync(h->cull_counters, 0, 8 * sizeof(uint32_t), h->stream));
     bpk::cull_blocks(h->stream, (int8_t *)h->grid, h->g, h->cg, h->cull_views_d, n_cull, kCullFirstViews, live_order_morton() ? 1 : 0,
-                     env_int("BP_LPT", 1), h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters);
+                     env_int("BP_LPT", 1), h->blk_dead, h->blk_cand, h->blk_live, h->cull_counters, h->lazy_unseen);
+    h->lazy_unseen = false;  // the first pass has written every block of the grid
     CU(cudaGetLastError());
     h->launches += (n_cull > kCullFirstViews) ? 2 : 1;
     // the first views over every surviving patch; the remaining views of the patches still alive, cut into segments
@@ -539,6 +542,8 @@ int process_impl(bp_handle *h, int32_t n, const float *cams, const void *const *
                 rc = launch_cull_carve(h, batch, hw, order.data() + v0, cams, work);
                 if (rc) return rc;
             } else {
+                rc = settle_seed(h);  // (no cull pass to seed the state for this launch)
+                if (rc) return rc;
                 bpk::carve(grd, h->stream, (int8_t *)h->grid, batch, (const ViewParams *)h->views_d[0], h->g, work);
             }
         } else {

@@ -249,6 +249,52 @@ def test_view_segments_default_value_and_chunks(BP, Oracle):
             bp.close()
 
 
+@pytest.mark.parametrize("shape", [(9, 17, 33), (16, 8, 47), (23, 31, 64), (8, 8, 16)])
+def test_lazy_clear_leaves_no_stale_state(BP, Oracle, shape):
+    """``clear`` does not write the state when a block cull will (the first pass of the next launch writes every block:
+    zeros over the blocks it writes off, "unseen" over the others).  Whatever looks at the state first must see a
+    cleared grid: a second scan after a first one, ``get_values`` / the raw state right after ``clear``, the kernel
+    without a cull, the per-view path - on shapes that are not multiples of the block or of the row padding."""
+    w, views = synth_scene("C5", 0.06, n_views=24)
+    org, vs = w["origin"], w["voxel_size"] * w["shape"][0] / max(shape)
+    for lazy in (1, 0):
+        with env(BP_LAZY_CLEAR=lazy):
+            bp = BP(list(shape), org, vs, default_value=-3)
+            ora = Oracle(list(shape), org, vs, type="carving", default_value=-3)
+            for v in views[:12]:
+                ora.process_view(*v)
+            first = ora.get_values().copy()
+            bp.process_views(views[:12])
+            np.testing.assert_array_equal(bp.get_values(), first)
+            # right after clear: an untouched grid, through every reader
+            bp.clear()
+            assert (bp.get_values() == -3).all()
+            bp.clear()
+            st = bp.state_tensor()
+            bp.sync()
+            assert int((st != 2).sum().item()) == 0
+            bp.clear()
+            tail, lo, hi = bp.get_values_tail()
+            assert lo == hi == -3 and (tail == -3).all()
+            # a second scan must not see anything of the first (other views carve other voxels)
+            ora2 = Oracle(list(shape), org, vs, type="carving", default_value=-3)
+            for v in views[12:]:
+                ora2.process_view(*v)
+            second = ora2.get_values()
+            bp.clear()
+            bp.process_views(views[12:])
+            np.testing.assert_array_equal(bp.get_values(), second, err_msg=f"fused, lazy {lazy}")
+            bp.clear()
+            for v in views[12:]:
+                bp.process_view(*v)
+            np.testing.assert_array_equal(bp.get_values(), second, err_msg=f"view by view, lazy {lazy}")
+            bp.clear()
+            with env(BP_CARVE_CULL=0):
+                bp.process_views(views[12:])
+            np.testing.assert_array_equal(bp.get_values(), second, err_msg=f"no cull, lazy {lazy}")
+            bp.close()
+
+
 def test_cull_on_striped_and_slab_handles(BP, Oracle):
     """Plane-sharded handles: a cull block of 8 LOCAL planes spans non-contiguous global planes under stripes narrower
     than a block; the bounds must still contain every voxel."""
