@@ -31,8 +31,9 @@ def main():
     combos = [dict(BP_ITEM_GRAB=g, BP_LPT=l, BP_LIVE_ORDER=1, BP_PACK_HEAD="auto", BP_VIEW_SPLIT=sp)
               for g, l, sp in ((1, 1, 16), (1, 1, 1000), (4, 1, 16), (2, 1, 16), (1, 0, 16), (1, 1, 8), (1, 1, 32))]
     if os.environ.get("PROBE_SPLITS"):  # short sweep: grab 1, LPT on, the given view splits
-        combos = [dict(BP_ITEM_GRAB=1, BP_LPT=1, BP_LIVE_ORDER=1, BP_PACK_HEAD=hd, BP_VIEW_SPLIT=int(sp))
-                  for sp in os.environ["PROBE_SPLITS"].split(",") for hd in os.environ.get("PROBE_HEADS", "auto").split(",")]
+        combos = [dict(BP_ITEM_GRAB=int(gr), BP_LPT=1, BP_LIVE_ORDER=1, BP_PACK_HEAD=hd, BP_VIEW_SPLIT=int(sp))
+                  for sp in os.environ["PROBE_SPLITS"].split(",") for hd in os.environ.get("PROBE_HEADS", "auto").split(",")
+                  for gr in os.environ.get("PROBE_GRABS", "1").split(",")]
     print("world  grab lpt split head | step_ms kernel_ms ingest_ms")
     for world in worlds:
         for c in combos:
