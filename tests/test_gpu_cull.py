@@ -61,22 +61,25 @@ def oracle_volume(Oracle, w, views, default_value=0, shape=None):
 
 @pytest.mark.parametrize("name,scale", [("C5", 0.125), ("C2", 0.3), ("C4", 0.2)])
 def test_cull_equals_no_cull_equals_oracle(BP, Oracle, name, scale):
+    """Cull off / on with both passes (every packed view: BP_CULL_VIEWS=32) / on as a grid of this size gets it by
+    default (the first pass only: few blocks) / on with 7 views - all equal to the oracle."""
     w, views = synth_scene(name, scale)
     want = oracle_volume(Oracle, w, views)
-    got = {}
-    for cull in (1, 0):
-        with env(BP_CARVE_CULL=cull):
+    for cull, n_views in ((1, 32), (1, None), (1, 7), (0, None)):
+        kv = {"BP_CARVE_CULL": cull}
+        if n_views:
+            kv["BP_CULL_VIEWS"] = n_views
+        with env(**kv):
             bp = BP(w["shape"], w["origin"], w["voxel_size"])
             bp.process_views(views)
-            got[cull] = bp.get_values().copy()
+            got = bp.get_values().copy()
             _, blocks, dead = bp.work_stats()
             bp.close()
-        if cull:  # (C4's cylinder fills a third of its box and the box fills the pictures: few blocks can go)
+        if cull and n_views == 32:  # (C4's cylinder fills a third of its box and the box fills the pictures: few blocks can go)
             assert blocks > 0 and dead > (0.3 if name == "C5" else 0.02) * blocks, f"the cull wrote off only {dead} of {blocks} blocks"
-        else:
+        elif not cull:
             assert dead == 0
-    assert np.array_equal(got[1], want), f"{(got[1] != want).sum()} voxels differ from the oracle with the cull on"
-    assert np.array_equal(got[0], want), f"{(got[0] != want).sum()} voxels differ from the oracle with the cull off"
+        assert np.array_equal(got, want), f"{(got != want).sum()} voxels differ from the oracle (cull {cull}, views {n_views})"
 
 
 @pytest.mark.parametrize("shape", [[9, 9, 33], [8, 8, 32], [17, 7, 95], [1, 1, 1], [3, 70, 31], [40, 12, 200]])

@@ -1,5 +1,5 @@
 #!/bin/bash
-# Round 2, thirteenth GPU call (1 GPU): whole GPU suite, smoke, default bench line, reference arm, launch list, and fresh
+# Round 2, thirteenth (and final-evidence) GPU call (1 GPU): whole GPU suite, smoke, default bench line, reference arm, launch list, and fresh
 # --set full captures of carve_items_kernel, carve_segments_kernel and average_kernel<u8> on the final kernels.
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log; tail -4 gpurun_out/pytest_gpu.log

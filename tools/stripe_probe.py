@@ -34,6 +34,8 @@ def main():
         combos = [dict(BP_ITEM_GRAB=int(gr), BP_LPT=1, BP_LIVE_ORDER=1, BP_PACK_HEAD=hd, BP_VIEW_SPLIT=int(sp))
                   for sp in os.environ["PROBE_SPLITS"].split(",") for hd in os.environ.get("PROBE_HEADS", "auto").split(",")
                   for gr in os.environ.get("PROBE_GRABS", "1").split(",")]
+        if os.environ.get("PROBE_CULLS"):
+            combos = [dict(c, BP_CULL_VIEWS=int(cv)) for c in combos for cv in os.environ["PROBE_CULLS"].split(",")]
     print("world  grab lpt split head | step_ms kernel_ms ingest_ms")
     for world in worlds:
         for c in combos:
@@ -60,7 +62,7 @@ def main():
             bp.sync()
             torch.cuda.synchronize()
             k_ms, i_ms, _ = bp.timing()
-            print(f"{world:5d}  {c['BP_ITEM_GRAB']:4} {c['BP_LPT']:3} {c['BP_VIEW_SPLIT']:5} {str(c['BP_PACK_HEAD']):>4} | "
+            print((f"cull {c['BP_CULL_VIEWS']:2} " if 'BP_CULL_VIEWS' in c else "") + f"{world:5d}  {c['BP_ITEM_GRAB']:4} {c['BP_LPT']:3} {c['BP_VIEW_SPLIT']:5} {str(c['BP_PACK_HEAD']):>4} | "
                   f"{e0.elapsed_time(e1) / steps:7.3f} {k_ms / steps:9.3f} {i_ms / steps:9.3f}", flush=True)
             bp.close()
 
