@@ -221,7 +221,7 @@ def test_view_segments_and_scheduling_switches(BP, Oracle, split, grab, lpt):
     want2 = oracle_volume(Oracle, w2, views2)
     md = torch.from_numpy(speckle).cuda()
     hw = np.tile(np.array([[w2["H"], w2["W"]]], dtype=np.int32), (n, 1))
-    with env(BP_VIEW_SPLIT=split, BP_ITEM_GRAB=grab, BP_LPT=lpt):
+    with env(BP_VIEW_SPLIT=split, BP_VIEW_SPLIT_MIN_REST=1, BP_ITEM_GRAB=grab, BP_LPT=lpt):
         bp = BP(w["shape"], w["origin"], w["voxel_size"])
         bp.process_views(views)
         got = bp.get_values().copy()
@@ -245,7 +245,7 @@ def test_view_segments_default_value_and_chunks(BP, Oracle):
     one_mask = views[0][3].nbytes
     for d in (0, -3):
         want = oracle_volume(Oracle, w, views, default_value=d)
-        with env(BP_VIEW_SPLIT=4, BP_STAGE_BYTES=20 * one_mask):
+        with env(BP_VIEW_SPLIT=4, BP_VIEW_SPLIT_MIN_REST=1, BP_STAGE_BYTES=20 * one_mask):
             bp = BP(w["shape"], w["origin"], w["voxel_size"], default_value=d)
             bp.process_views(views)
             np.testing.assert_array_equal(bp.get_values(), want, err_msg=f"default {d}")
