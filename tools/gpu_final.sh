@@ -1,14 +1,13 @@
 #!/bin/bash
-# One gpurun call at the end of a session: full parity suite, smoke, default bench, the tools of the 8f rows, and an
-# ncu launch list of those tools (kernel names + durations as evidence; numbers under ncu are not bench values).
+# Last call of a round (1 GPU): what the driver runs at round end - the GPU suite, smoke, the default bench line.
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
-python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"
-python tests/bench/bench_masks.py > gpurun_out/bench_masks.json 2> gpurun_out/bench_masks.err
-python tests/bench/bench_score_points.py 200000 > gpurun_out/bench_score_points.json 2> gpurun_out/bench_score.err
-python tests/bench/bench_task_tail.py > gpurun_out/bench_task_tail.json 2> gpurun_out/bench_tail.err
-ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_8f.csv \
-  -k regex:'minmax_kernel|threshold_kernel|dilate_kernel|expand_bits|score_points|finish_scores|tail_kernel' \
-  python __graft_entry__.py smoke > gpurun_out/ncu_8f.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cat gpurun_out/bench_default.json; cat gpurun_out/bench_masks.json gpurun_out/bench_score_points.json gpurun_out/bench_task_tail.json
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log
+python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench default rc=$?"; tail -2 gpurun_out/bench_default.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/bench_default.json'))
+print('N1 carve ms', d['ms_per_step'], 'kernel', d['roofline']['kernel_ms_per_launch'], 'e2e', d['e2e']['ms_per_step'], d['oracle_check'], 'frac', d['roofline']['frac'], 'ncu stale', (d['roofline'].get('ncu') or {}).get('stale'))
+a=d['averaging']; print('N1 avg ms', a['ms_per_step'], 'e2e', a['e2e']['ms_per_step'], a['oracle_check'])
+for k,c in d['configs'].items(): print(k, c['ms_per_step'], c['value'], c['e2e']['ms_per_step'], c['oracle_check'], c['golden']['all'], c['roofline']['frac'])
+PY
