@@ -9,5 +9,5 @@ import json
 d=json.load(open('gpurun_out/bench_default.json'))
 print('N1 carve ms', d['ms_per_step'], 'kernel', d['roofline']['kernel_ms_per_launch'], 'e2e', d['e2e']['ms_per_step'], d['oracle_check'], 'frac', d['roofline']['frac'], 'ncu stale', (d['roofline'].get('ncu') or {}).get('stale'))
 a=d['averaging']; print('N1 avg ms', a['ms_per_step'], 'e2e', a['e2e']['ms_per_step'], a['oracle_check'])
-for k,c in d['configs'].items(): print(k, c['ms_per_step'], c['value'], c['e2e']['ms_per_step'], c['oracle_check'], c['golden']['all'], c['roofline']['frac'])
+for k,c in d['configs'].items(): print(k, c['ms_per_step'], c['value'], c['e2e']['ms_per_step'], c['oracle_check'], (c.get('golden') or {}).get('all'), c['roofline']['frac'])
 PY
