@@ -133,8 +133,10 @@ int launch_cull_carve(bp_handle *h, const Batch &batch, const int32_t *hw, const
     int n_cull = 0;
     // How many packed views the cull looks at (BP_CULL_VIEWS).  The first three write off 9 blocks in 10; the second
     // pass over the survivors saves the kernels 0.2 ms on the whole C5 grid and costs 0.05 ms of latency whatever the
-    // grid: a handle with few blocks (a plane-sharded rank) stops after the first (profiles/r02_cull_views_ab.txt).
-    const int cull_dflt = h->cg.n_blocks >= 200000u ? kCullViews : kCullFirstViews;
+    // grid: a handle with few blocks (a plane-sharded rank, a small scan) stops after the first
+    // (profiles/r02_cull_views_ab.txt: C5 rank of 8, 65 k blocks, 1.269 -> 1.220 ms; C2, 26 k blocks, 0.410 -> 0.369;
+    // but C1, 154 k blocks, 0.508 -> 0.677 without the second pass).
+    const int cull_dflt = h->cg.n_blocks >= 100000u ? kCullViews : kCullFirstViews;
     const int cull_cap = std::min(kCullViews, std::max(0, env_int("BP_CULL_VIEWS", cull_dflt)));
     while (n_cull < batch.n && n_cull < cull_cap && batch.v[n_cull].kind == 0) ++n_cull;  // the packed head
     size_t need = 0;
