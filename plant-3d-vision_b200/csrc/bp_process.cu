@@ -55,12 +55,12 @@ int pack_head_views(const bp_handle *h) {
         const int v = std::atoi(e);
         return v < 0 ? kMaxViews : v;
     }
-    // 16 views whatever the share of the grid the handle holds: since the later views run as view segments
+    // 16 views on a large handle, whatever its share of the grid: since the later views run as view segments
     // (carve_segments_kernel) the raw reads cost the kernels nothing measurable (C5, one GPU: kernels 7.07 ms with 16
     // views packed against 7.12 with all 240, and 0.06 instead of 0.73 ms of packing; with 32 / 64 packed views both
-    // the pack and the tile tables of the cull grow: profiles/r02_packhead_v2.txt).
-    (void)h;
-    return 16;
+    // the pack and the tile tables of the cull grow: profiles/r02_packhead_v2.txt).  A handle with few blocks packs
+    // only the views its cull looks at (launch_cull_carve): a C5 rank of 8 goes from 1.205 to 1.162 ms per step.
+    return (h->blk_dead && h->cg.n_blocks < 100000u) ? kCullFirstViews : 16;
 }
 
 // bit-pack ONE view whose raw mask already sits in device memory (general path: any dtype / width)
