@@ -87,6 +87,20 @@ def spread_order(cams):
     return order
 
 
+def carve_chunk_bounds(n, G, chunk_views):
+    """View ranges of the sharded carving ingest: [0, head) with head = 32 rounded up to a multiple of the world size
+    ``G``, then chunks of ``chunk_views`` (rounded down to a multiple of ``G``, at least ``G``); a last chunk shorter than
+    half a chunk is merged into the one before.  Returns the increasing list of bounds, first 0, last ``n``."""
+    head = min(n, -(-32 // G) * G)
+    if head >= n:
+        return [0, n]
+    step = max(G, (int(chunk_views) // G) * G)
+    bounds = [0] + list(range(head, n, step)) + [n]
+    if len(bounds) > 3 and bounds[-1] - bounds[-2] < step // 2:
+        del bounds[-2]
+    return bounds
+
+
 def bind_to_gpu_numa_node(device):
     """Pin this process (and therefore its first-touch / pinned host allocations) to the CPUs NVML reports as
     local to CUDA device ``device``.  With one rank per GPU, host<->device copies then stay on the GPU's own
@@ -252,11 +266,7 @@ class DistributedBackprojection(object):
             order = spread_order(cams)
             cams = cams[order]
             masks = [masks[v] for v in order]
-            head = min(n, -(-32 // G) * G)
-            step = max(G, (int(os.environ.get("BP_SHARD_CHUNK_VIEWS", self.CARVE_CHUNK_VIEWS)) // G) * G)
-            bounds = ([0] + list(range(head, n, step)) + [n]) if head < n else [0, n]
-            if len(bounds) > 3 and bounds[-1] - bounds[-2] < step // 2:
-                del bounds[-2]  # no short last chunk
+            bounds = carve_chunk_bounds(n, G, int(os.environ.get("BP_SHARD_CHUNK_VIEWS", self.CARVE_CHUNK_VIEWS)))
         else:
             # averaging: ~CHUNK_BYTES of maps per chunk, upload hidden behind the kernel; the caller's view order is kept
             per_chunk = max(1, self.CHUNK_BYTES // (H * W))

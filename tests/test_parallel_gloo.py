@@ -159,3 +159,24 @@ def test_voxels_task_over_a_distributed_engine(tmp_path, sharding):
         i0, i1 = z["i_range"]
         assert np.array_equal(z["part"], full[:, i0:i1])
         assert float(z["lo"]) == st1["min"] and float(z["hi"]) == st1["max"]
+
+
+def test_carve_chunk_bounds_cover_every_view_once():
+    """Chunks of the sharded carving ingest (parallel.py): contiguous, increasing, first 0 / last n, the first chunk the
+    32-view head (rounded up to the world size), later chunks multiples of the world size except possibly the last,
+    no short last chunk."""
+    from plant3dvision_b200.parallel import carve_chunk_bounds
+    for n in (0, 1, 5, 18, 31, 32, 33, 60, 72, 120, 240, 241, 1000):
+        for G in (1, 2, 3, 4, 8):
+            for chunk in (1, 7, 48, 64, 1000):
+                b = carve_chunk_bounds(n, G, chunk)
+                assert b[0] == 0 and b[-1] == n and all(x < y for x, y in zip(b, b[1:])) or (n == 0 and b == [0, 0]), (n, G, chunk, b)
+                if n > 0 and len(b) > 2:
+                    step = max(G, (chunk // G) * G)
+                    assert b[1] == -(-32 // G) * G
+                    assert all((y - x) % G == 0 for x, y in zip(b[1:-1], b[2:-1])), (n, G, chunk, b)
+                    assert all(y - x in (step, 2 * step) or y == n for x, y in zip(b[1:], b[2:])), (n, G, chunk, b)
+                    if len(b) > 3:
+                        assert b[-1] - b[-2] >= step // 2, (n, G, chunk, b)
+    assert carve_chunk_bounds(240, 8, 48) == [0, 32, 80, 128, 176, 240]
+    assert carve_chunk_bounds(18, 2, 48) == [0, 18]
