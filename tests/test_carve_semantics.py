@@ -87,3 +87,29 @@ def test_speculative_readback_invariant():
         assert not differs[~rows].any()
         host[differs] = lut[final[differs, :nz]]
         assert np.array_equal(host, lut[final[:, :nz]])
+
+
+def test_and_coding_of_the_view_segments_is_the_minimum():
+    """carve_segments_kernel merges the segments of one patch with an atomic AND on a transient coding of the states
+    (0 carved, 1 seen, 3 unseen instead of 2; bp_kernels.cu: classify_items_kernel / decode_items_kernel).  The claim it
+    rests on, byte-parallel as the kernels apply it on 32-bit words: decode(AND of encoded states) == minimum of the
+    states, for any number of operands - and the minimum over the views is what kernels/backprojection.c:65-83 computes."""
+    rng = np.random.default_rng(3)
+
+    def encode(w):
+        return w | ((w >> 1) & np.uint32(0x01010101))
+
+    def decode(w):
+        return w - ((w >> 1) & np.uint32(0x01010101))
+
+    for n_ops in (1, 2, 3, 7):
+        states = rng.integers(0, 3, size=(n_ops, 4096, 4), dtype=np.uint8)           # 4 voxels per word
+        words = states.view(np.uint32)[..., 0]                                        # [n_ops, 4096]
+        enc = encode(words)
+        assert set(np.unique(enc.view(np.uint8))) <= {0, 1, 3}
+        merged = np.bitwise_and.reduce(enc, axis=0)
+        got = decode(merged).view(np.uint8).reshape(-1, 4)
+        np.testing.assert_array_equal(got, states.min(axis=0))
+    # round trip on every byte value the state can hold, padding included (it holds 0, 1 or 2 as well)
+    w = np.array([0x00010200, 0x02020202, 0x01000102], dtype=np.uint32)
+    np.testing.assert_array_equal(decode(encode(w)), w)
